@@ -1,0 +1,311 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json's metric for the per-substep RHS path.
+
+  metric : MHD cell-updates/s (RK3 substep), i.e. nx*ny*nz*3 cell-substep-updates per full step
+  config : periodic MHD with entropy 512^3 (8 variables, FP64); z-slab decomposed over N GPUs
+           (strong scaling: the global grid is fixed)
+  step   : one full 2N-RK3 time step (3 fused rhs+update substeps, fixed dt) on synthetic data
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--n 512] [--impl b200|reference]
+
+One JSON line on stdout (rank 0).  `value` is device-resident throughput, `e2e` goes through the
+reference-facing module-GPU calls with HOST buffers (load_farray_to_GPU + 3 x rhs_GPU +
+copy_farray_from_GPU every step), `roofline` is measured with CUDA events around the fused kernel,
+`cpu_baseline` times the CPU oracle (a restatement, not the Fortran binary: no gfortran here).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "MHD cell-updates/s (RK3 substep)"
+UNIT = "cell-substep-updates/s"
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """samples nvidia-smi during the timed region (B200_PROFILING.md clocks line)"""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, pw = [], [], set(), []
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_oracle_throughput(n, steps, nthreads=0):
+    """cell-substep-updates/s of the CPU restatement (-O3 -march=native, OpenMP over (m,n) pencils)
+    on an n^3 periodic sample of the same 8-variable physics."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import numpy as np
+    import pc_oracle
+    from pencil_code_b200 import config as pcfg
+    from pencil_code_b200 import synthetic
+    cfg = pcfg.config_mhd_entropy(n)
+    outdir = tempfile.mkdtemp(prefix="pc_oracle_fast_")  # -march=native must be built on the box that runs it
+    o = pc_oracle.Oracle(cfg, nthreads=nthreads, fast=True, outdir=outdir)
+    f = synthetic.initial_condition(cfg)
+    df = np.zeros_like(f)
+    dt, t = pcfg.fixed_dt(cfg), 0.0
+    o.time_step(f, df, False, dt, t)  # warm-up (page faults, thread pool)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        dt, t, _ = o.time_step(f, df, False, dt, t)
+    el = time.perf_counter() - t0
+    ncores = nthreads if nthreads > 0 else (os.cpu_count() or 1)
+    return n ** 3 * 3 * steps / el, el, ncores
+
+
+def run_reference(args, rank):
+    """--impl reference: the reference's CPU implementation of the path.  The Fortran code cannot be
+    compiled in this image (no gfortran/MPI), so this times the CPU oracle (restatement) with all host
+    threads on a bounded sample (128^3, same physics) of the workload."""
+    if rank != 0:
+        return
+    n = 128
+    per_step = []
+    for _ in range(max(args.warmup, 0)):
+        pass  # warm-up is inside cpu_oracle_throughput
+    val, el, cores = cpu_oracle_throughput(n, max(args.steps, 1))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": el / max(args.steps, 1) * 1e3, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "periodic MHD with entropy %d^3 (8 vars, FP64), fixed dt" % args.n,
+                   "sample": "%d^3 periodic box, same physics, per step" % n},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "%d^3 x %d RK3 steps, CPU restatement (oracle, g++ -O3 -march=native -fopenmp); "
+                                   "the Fortran reference cannot be built here (no gfortran/MPI)" % (n, args.steps)},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--n", type=int, default=512)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--kernel-variant", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3  # timing rule: W >= 3
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            sys.exit("bench.py --gpus %d must be launched with torchrun (one rank per GPU)" % args.gpus)
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from pencil_code_b200 import config as pcfg
+    from pencil_code_b200 import synthetic
+    from pencil_code_b200.gpu import GPU, nccl_unique_id
+
+    if not torch.cuda.is_available():
+        sys.exit("bench.py: no CUDA device; the gpu_b200 module has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    nccl = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group(backend="nccl", device_id=dev)
+        ids = [nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        nccl = (ids[0], rank, world)
+
+    n = args.n
+    cfg = pcfg.config_mhd_entropy(n, nprocz=world, ipz=rank)
+    cfg["device"] = local_rank
+    cfg["kernel_variant"] = args.kernel_variant
+    nvar = cfg["nvar"]
+    dt = pcfg.fixed_dt(cfg)
+    cells_global = n ** 3
+    shape = synthetic.farray_shape(cfg)
+    nbytes_f = int(np.prod(shape)) * 8
+
+    # host f-array in pinned memory (what the Fortran driver owns)
+    fh_t = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+    fh = fh_t.numpy()
+    fh[...] = 0.0
+
+    g = GPU(cfg, nccl=nccl)
+    stream = torch.cuda.Stream(device=dev)  # a real (non-default) stream so that torch events see the library's work
+    torch.cuda.set_stream(stream)
+    g.L.pcb200_set_stream(stream.cuda_stream)
+    g.register_GPU()
+    g.initialize_GPU(fh, nt=0)
+    g.init_synthetic(12345)  # synthetic forced-turbulence-like state generated on the device
+    g.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(t):
+        return g.time_step(fh, dt, False, t)
+
+    t = 0.0
+    for _ in range(args.warmup):
+        _, t = step(t)
+    # ---- device-resident timing
+    g.enable_kernel_timing(True)
+    g.kernel_timing(reset=True)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    l0 = g.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        _, t = step(t)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = g.launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    kms, klaunch = g.kernel_timing(reset=True)
+    g.enable_kernel_timing(False)
+    tmax = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms = float(tmax.item())
+    value = cells_global * 3 * args.steps / (ms * 1e-3)
+
+    # ---- end-to-end through the module-GPU calls with host buffers (H2D + 3 substeps + D2H per step)
+    g.copy_farray_from_GPU(fh)
+    barrier()
+    t_e2e0 = time.perf_counter()
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record(stream)
+    for _ in range(args.e2e_steps):
+        g.load_farray_to_GPU(fh)
+        _, t = step(t)
+        g.copy_farray_from_GPU(fh)
+    e3.record(stream)
+    barrier()
+    ms_e2e = max(e2.elapsed_time(e3), (time.perf_counter() - t_e2e0) * 1e3)
+    tm2 = torch.tensor([ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tm2, op=dist.ReduceOp.MAX)
+    ms_e2e = float(tm2.item())
+    e2e_value = cells_global * 3 * args.e2e_steps / (ms_e2e * 1e-3)
+    finite = bool(np.isfinite(fh[:, 3:-3, 3:-3, 3:-3]).all())
+
+    # ---- roofline of the dominant kernel (fused rhs+rk), measured live with CUDA events
+    peak, peak_src = hbm_peak()
+    cells_local = cfg["nx"] * cfg["ny"] * cfg["nz"]
+    bytes_per_launch = cells_local * 80.0 * nvar / 3.0  # 80*nvar B per cell per full step
+    avg_kernel_ms = kms / max(klaunch, 1)
+    achieved = bytes_per_launch / (avg_kernel_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "rhs_update (fused RHS + 2N-RK3)", "avg_kernel_ms": avg_kernel_ms,
+                "kernel_launches": klaunch, "kernel_share_of_step": kms / ms if ms > 0 else None,
+                "algorithmic_bytes_per_launch": bytes_per_launch, "peak_source": peak_src,
+                "frac_of_nominal_8TBs": achieved / 8000.0}
+    traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(traffic_file):
+        try:
+            roofline["traffic"] = json.load(open(traffic_file)).get("dram_bytes_per_launch_512")
+        except Exception:
+            pass
+
+    g.finalize_GPU()
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, el, cores = cpu_oracle_throughput(128, 2)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                        "sample": "128^3 periodic box, same 8-variable physics, 2 RK3 steps (%.1f s); CPU restatement "
+                                  "(oracle) with g++ -O3 -march=native -fopenmp, not the Fortran binary" % el}
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "periodic MHD with entropy %d^3 (8 vars, FP64), fixed dt, 2N-RK3" % n,
+                       "decomposition": "1x1x%d z-slabs" % world, "nvar": nvar,
+                       "l2": "inputs larger than L2 (%.1f GB per f buffer per GPU)" % (nbytes_f / 1e9),
+                       "kernel_variant": args.kernel_variant, "finite": finite},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes_f * world,
+                    "d2h_bytes_per_step": nbytes_f * world, "steps": args.e2e_steps,
+                    "ms_per_step": ms_e2e / args.e2e_steps,
+                    "path": "load_farray_to_GPU + 3 x rhs_GPU + copy_farray_from_GPU per step, pinned host f-array"},
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "roofline": roofline,
+            "cpu_baseline": cpu_baseline,
+            "us_per_point_per_step": ms * 1e3 / args.steps / cells_global,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

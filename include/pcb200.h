@@ -1,0 +1,174 @@
+/*
+ * pcb200.h -- C ABI of libpcb200.so, the B200-native GPU module for Pencil Code
+ * (selected with GPU=gpu_b200 in src/Makefile.local).
+ *
+ * Part 1 are the entry points the reference's Fortran `module GPU`
+ * (src/gpu.h:1-12; src/gpu_astaroth.f90:21-53 `external *_c`) binds; names,
+ * argument order and by-reference convention are those of
+ * src/gpu_astaroth_ansi.c / src/astaroth/gpu_astaroth.cc.  Every symbol is
+ * exported twice: plain (for ISO_C_BINDING `bind(C,name=...)`) and with a
+ * trailing underscore (the reference's FTNIZE() convention,
+ * src/headers_c.h:31-37).
+ *
+ * Part 2 replaces what the reference obtains at compile time from
+ * cparam_c.h (scripts/cparam2c) and at run time from the pushpars2c address
+ * tables (src/global_pushpars.f90:26-101 and each module's pushpars2c): one
+ * plain struct handed over before initialize_gpu_c.
+ *
+ * Error convention (as gpu_astaroth.cc:1595-1597,2074-2078): no status codes;
+ * an unsupported configuration or a CUDA/NCCL error prints to stderr and
+ * aborts the process.  There is NO CPU fallback.
+ */
+#ifndef PCB200_H
+#define PCB200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ */
+/* Part 2: configuration                                               */
+/* ------------------------------------------------------------------ */
+typedef struct pcb200_config {
+  /* local interior sizes per rank and decomposition (cparam.f90:54-75; cparam.local) */
+  int nx, ny, nz;
+  int nprocx, nprocy, nprocz; /* nprocx must be 1 */
+  int ipx, ipy, ipz;          /* this rank's position */
+  int nvar;                   /* mvar */
+  int iux, ilnrho, iss, iax;  /* 0-based slots (Fortran index-1); -1 = module absent */
+  double dx, dy, dz;          /* equidistant Cartesian (grid.f90:123-149) */
+  double x0, y0, z0;          /* x(l1), y(m1), z(n1) of THIS rank */
+  /* eos_idealgas pushpars (eos_idealgas.f90:4589-4606) */
+  double cs20, gamma, cp, lnrho0;
+  double mu0; /* cdata (global_pushpars.f90: mu0) */
+  /* viscosity.f90:3250-3255 */
+  double nu, nu_hyper3;
+  int lvisc_nu_const, lvisc_hyper3_simplified, lvisc_hyper3_nu_const;
+  /* density.f90:4591-4599 */
+  double diffrho_hyper3;
+  int ldiff_hyper3lnrho;
+  /* entropy.f90:8675-8816 */
+  double chi;
+  int lheatc_chiconst, lviscosity_heat;
+  /* magnetic.f90:12063-12069 */
+  double eta;
+  int lresi_eta_const, lohmic_heat, llorentzforce;
+  /* upwinding: hydro.f90:9367, density.f90:4591-4599, entropy.f90, magnetic.f90 */
+  int lupw_uu, lupw_lnrho, lupw_ss, lupw_aa;
+  /* cdata: cdt, cdtv, cdtv2, cdtv3 (global_pushpars.f90:27-32), dtmax */
+  double cdt, cdtv, cdtv2, cdtv3;
+  double dtmax;
+  /* boundary conditions: only 'p' (periodic) in all directions is supported */
+  int lperi[3];
+  /* device selection: -1 = local rank modulo device count */
+  int device;
+  /* kernel selection: 0 = auto (fastest validated), 1 = reference-order global-load kernel,
+     2 = shared-memory z-marching kernel */
+  int kernel_variant;
+} pcb200_config;
+
+/* must be called before initialize_gpu_c; copies *cfg */
+void pcb200_configure(const pcb200_config *cfg);
+int pcb200_sizeof_config(void);
+
+/* Timestep exchange with the host driver.  The Fortran module calls
+   pcb200_set_dt before rhs_gpu_c when ldt=F, and pcb200_get_dt1_max after
+   substep 1 when ldt=T to feed Sub::set_dt (sub.f90:4223-4254). */
+void pcb200_set_dt(const double *dt, const int *ldt);
+void pcb200_get_dt1_max(double *dt1_max);
+void pcb200_get_dt(double *dt);
+
+/* helical forcing coefficients for the step in progress (forcing.f90:1731-1746
+   forcing_pars_hel; consumed after substep 3, astaroth/forcing.h:1-36).
+   lforce=0 disables. */
+void pcb200_set_forcing_hel(const int *lforce, const double coef1[3], const double coef2[3],
+                            const double fda[3], const double kk[3], const double *phase,
+                            const double *fact, const double *k1_ff);
+
+/* ask for time-series diagnostics to be reduced during the next substep 1
+   (ldiagnos=lfirst.and.lout, equ.f90:120) */
+void pcb200_request_diagnostics(void);
+
+/* multi-GPU: NCCL bootstrap without MPI.  Rank 0 obtains an id (128 bytes),
+   the host broadcasts it (MPI_Bcast in Fortran, torch.distributed in bench.py),
+   every rank calls pcb200_nccl_init before initialize_gpu_c. */
+void pcb200_nccl_get_unique_id(char id[128]);
+void pcb200_nccl_init(const char id[128], const int *rank, const int *nranks);
+
+/* use an externally owned CUDA stream (cudaStream_t as void*) for all work; NULL = own stream */
+void pcb200_set_stream(void *cuda_stream);
+/* block until all queued device work has finished */
+void pcb200_synchronize(void);
+/* device-side synthetic initial condition written straight into the device f-array */
+void pcb200_init_synthetic(const int *seed);
+/* number of kernels this library has launched so far (bench.py: gpu_launches) */
+long long pcb200_launch_count(void);
+/* device time in ms spent in the fused rhs+rk kernel since the last reset, and its launch count */
+void pcb200_kernel_timing(double *ms, long long *launches, const int *reset);
+void pcb200_enable_kernel_timing(const int *on);
+
+/* ------------------------------------------------------------------ */
+/* Part 1: the reference's GPU-module C interface                       */
+/* ------------------------------------------------------------------ */
+/* gpu_astaroth.cc:2009-2122 initializeGPU; RETAINS f for load/copy */
+void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, int *lread_all_vars_from_device,
+                      int *lcpu_timestep_on_gpu, int *lac_sparse_autotuning);
+void register_gpu_c(void);
+void finalize_gpu_c(void);
+/* gpu_astaroth.cc:1672-1717 substepGPU: ghost exchange + RHS + 2N-RK update (+forcing after 3) */
+void rhs_gpu_c(int *isubstep, double *t);
+void before_boundary_gpu_c(int *lrmv, int *isubstep, double *t, int *lsubstepping);
+void update_after_substep_gpu_c(void);
+/* gpu_astaroth.cc:1947-1971 loadFarray (uses the retained pointer) / :1719-1814 copyFarray */
+void load_farray_c(void);
+void copy_farray_c(double *f);
+void gpu_prepare_for_first_substep_c(double *t);
+/* gpu_astaroth.cc:1833-1849 copyVBApointers */
+void get_farray_ptr_gpu_c(double **p_in, double **p_out);
+void reload_gpu_config_c(void);
+/* gpu_astaroth.cc:2179-2241 updateInConfig* ; return index>=0 or -1 if unknown */
+int update_on_gpu_scal_by_name_c(const char *name, double *value);
+int update_on_gpu_vec_by_name_c(const char *name, double *value);
+int update_on_gpu_arr_by_name_c(const char *name);
+void update_on_gpu_scal_by_ind_c(int *index, double *value);
+void update_on_gpu_vec_by_ind_c(int *index, double *value);
+void update_on_gpu_arr_by_ind_c(int *index);
+void *pos_real_ptr_c(void **ptr, int *ind);
+void split_update_gpu_c(double *f);
+void radtransfer_gpu_c(void);
+void test_bcs_c(void);
+
+/* gpu.h:12 n_gpu_reduced_vars=20.  Slot layout of dst[]: */
+enum {
+  PCB200_RED_URMS = 0, PCB200_RED_UMAX, PCB200_RED_RHOM, PCB200_RED_BRMS, PCB200_RED_BMAX,
+  PCB200_RED_JRMS, PCB200_RED_JMAX, PCB200_RED_ABM, PCB200_RED_JBM, PCB200_RED_OUM,
+  PCB200_RED_EPSK, PCB200_RED_SSM, PCB200_RED_DTU, PCB200_RED_DTC, PCB200_RED_DTB,
+  PCB200_RED_DTNU, PCB200_RED_DT1MAX, PCB200_RED_DT, PCB200_RED_SPARE0, PCB200_RED_SPARE1,
+  PCB200_N_REDUCED = 20
+};
+void get_gpu_reduced_vars_c(double *dst);
+
+/* ------------------------------------------------------------------ */
+/* Part 3: host-side mirror of the reference driver for this path       */
+/* (time_step/advance_substeps with lgpu=T: timestep.f90:206-270,       */
+/*  77-204; pde: equ.f90:106-120,197-201,307-332; run.f90:575)          */
+/* ------------------------------------------------------------------ */
+typedef struct pcb200_driver_state {
+  double t, dt;
+  int it, ldt;     /* ldt = (dt==0) at start: timestep.f90:60-75 */
+  int lforcing;    /* iforce='helical' */
+  double force, relhel, kav; /* forcing_run_pars */
+  int nk;          /* number of wave vectors in k-list */
+  const double *kkx, *kky, *kkz;
+  unsigned long long rng_state; /* host RNG for fconst_coefs_hel */
+  int it1;         /* diagnostics cadence (run_pars it1) */
+} pcb200_driver_state;
+
+/* advance nt steps; if ts_rows!=NULL, writes one row of PCB200_N_REDUCED+2 doubles
+   (it, t, reduced vars) for every step with mod(it-1,it1)==0; returns rows written */
+int pcb200_driver_run(pcb200_driver_state *st, int nt, double *ts_rows, int max_rows);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

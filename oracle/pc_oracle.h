@@ -1,0 +1,107 @@
+/*
+ * pc_oracle.h -- C interface of the CPU ORACLE (test infrastructure only).
+ *
+ * The oracle is a plain C++ restatement of Pencil Code's per-substep RHS
+ * evaluation (pde -> rhs_cpu -> calc_all_pencils/calc_all_rhs -> set_dt1_max)
+ * and the 2N-RK3 update of timestep.f90, in the reference's pencil order.
+ * It is NOT part of the product: only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs may load it.
+ *
+ * Parity status: the Fortran reference cannot be compiled in this image
+ * (no gfortran, no MPI), so tight (1e-12) parity is pinned by this
+ * restatement only; against the reference's own artefacts it is pinned by
+ *   - python/pencil/math/derivatives/der_6th_order_w_ghosts.py (imported from
+ *     /root/reference when generating tests/golden/deriv_golden.npz),
+ *   - the closed-form it=0 row of samples/gputest/cpu-test.out:273
+ *     (urms, umax, rhom, epsK) -- see tests/test_oracle_golden.py.
+ * => "parity coarsely pinned" (SURVEY.md section 8c).
+ *
+ * Layout: f[ivar][iz][iy][ix], x fastest, mx=nx+6 etc. (src/cdata.f90:90-92).
+ */
+#ifndef PC_ORACLE_H
+#define PC_ORACLE_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pc_oracle_pars {
+  /* local interior grid and variables (cparam.f90:54-75) */
+  int nx, ny, nz;
+  int nvar;
+  int iux, ilnrho, iss, iax; /* 0-based slot of first component, -1 = module absent */
+  double dx, dy, dz;
+  double x0, y0, z0; /* coordinate of first interior point: x(l1), y(m1), z(n1) */
+  /* eos_idealgas.f90:46-47,154-270 */
+  double cs20, gamma, cp, lnrho0;
+  /* cdata.f90:64 */
+  double mu0;
+  /* viscosity.f90:1633-1664,1982-1989,2250-2257 */
+  double nu, nu_hyper3;
+  int lvisc_nu_const, lvisc_hyper3_simplified, lvisc_hyper3_nu_const;
+  /* density.f90:3197-3288 */
+  double diffrho_hyper3;
+  int ldiff_hyper3lnrho;
+  /* entropy.f90:4852-4947, viscosity.f90:2743-2789 */
+  double chi;
+  int lheatc_chiconst, lviscosity_heat;
+  /* magnetic.f90:5584-5590,6138-6144 */
+  double eta;
+  int lresi_eta_const, lohmic_heat, llorentzforce;
+  /* upwinding switches: hydro.f90:286, density.f90:122, entropy.f90:139, magnetic.f90:359 */
+  int lupw_uu, lupw_lnrho, lupw_ss, lupw_aa;
+  /* cdata.f90:235-239 */
+  double cdt, cdtv, cdtv2, cdtv3;
+  double dtmax; /* equ.f90:270-280: dt1_max initialised to 1/dtmax */
+  int nthreads; /* OpenMP threads over (m,n) pencils; <=0 -> default */
+} pc_oracle_pars;
+
+/* helical forcing coefficients for one step (forcing.f90:1773-2001) */
+typedef struct pc_oracle_forcing {
+  double coef1[3], coef2[3], fda[3], kk[3];
+  double phase, fact;
+  double k1_ff;
+} pc_oracle_forcing;
+
+/* diagnostics accumulated during substep 1 */
+typedef struct pc_oracle_diag {
+  double urms, umax, rhom, brms, bmax, jrms, jmax, abm, jbm, oum, epsK, ssm;
+  double dtu, dtc, dtb, dtnu; /* max(advec_uu)/cdt etc. (not yet multiplied by dt) */
+  double dt1_max;
+} pc_oracle_diag;
+
+/* periodic ghost fill in x, then y, then z (boundcond.f90:2387-2433) */
+void pc_oracle_update_ghosts(const pc_oracle_pars *p, double *f);
+
+/* one derivative of variable k along j (1..3) for the whole interior; out is nx*ny*nz.
+   kind: 1=der, 2=der2, 5=der5, 6=der6, 7=der6 upwind; for kind 12/23/31 mixed derij. */
+void pc_oracle_deriv(const pc_oracle_pars *p, const double *f, int k, int j, int kind, double *out);
+
+/* df(interior) += RHS(f); ghosts of f must be valid.  Returns max dt1 (0 if !lcourant).
+   diag may be NULL. */
+double pc_oracle_rhs(const pc_oracle_pars *p, const double *f, double *df, int lcourant,
+                     pc_oracle_diag *diag);
+
+/* one substep: ghosts, df=alpha*df (or 0), rhs, optional dt from CFL (itsub==1 && ldt),
+   f += dt*beta*df.  *dt is in/out. */
+void pc_oracle_substep(const pc_oracle_pars *p, double *f, double *df, int itsub, int ldt,
+                       double *dt, double *t, pc_oracle_diag *diag);
+
+/* full RK3 step (timestep.f90:206-270) + optional forcing (run.f90:575) */
+void pc_oracle_time_step(const pc_oracle_pars *p, double *f, double *df, int ldt, double *dt,
+                         double *t, const pc_oracle_forcing *frc, pc_oracle_diag *diag);
+
+/* u += Re((coef1 + i coef2) fx fy fz) (forcing.f90:2170-2345) */
+void pc_oracle_forcing_hel(const pc_oracle_pars *p, double *f, const pc_oracle_forcing *frc);
+
+/* host-side coefficient generation (forcing.f90:1773-2001) given k-vector, phase and phi */
+void pc_oracle_forcing_coefs(double force, double relhel, double kav, double cs0eff, double dt,
+                             const double kvec[3], double phase, double phi,
+                             pc_oracle_forcing *out);
+
+int pc_oracle_sizeof_pars(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,938 @@
+// pcb200.cu -- kernels, device state and the C ABI of libpcb200.so (sm_100a only).
+//
+// Boundary mirrored: Pencil Code `module GPU` C interface
+// (/root/reference/src/gpu_astaroth.f90:21-53, gpu_astaroth_ansi.c, astaroth/gpu_astaroth.cc).
+// See include/pcb200.h for the contract and DESIGN.md for the data layout.
+#include "pcb200_device.cuh"
+#include "../../include/pcb200.h"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <dlfcn.h>
+#include <vector>
+
+namespace pcb200 {
+
+
+// ---------------------------------------------------------------------------
+// error handling: print + abort (gpu_astaroth.cc:1595-1597)
+// ---------------------------------------------------------------------------
+[[noreturn]] static void die(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  std::fprintf(stderr, "pcb200: FATAL: ");
+  std::vfprintf(stderr, fmt, ap);
+  std::fprintf(stderr, "\n");
+  va_end(ap);
+  std::fflush(stderr);
+  std::abort();
+}
+#define CK(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) die("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
+  } while (0)
+
+// ---------------------------------------------------------------------------
+// Kernel 1 (variant 1): fused RHS + 2N-RK3 update, one cell per thread, taps through L1/L2.
+// ---------------------------------------------------------------------------
+struct UpdateArgs {
+  const double *fin;
+  double *fout;
+  double *df;
+  const double *dt_dev; // dt of this step (device resident)
+  double alpha, beta;
+  int read_df, write_df;
+  int z_lo, z_hi; // interior z range handled (indices incl. ghosts)
+  Forcing frc;
+};
+
+template <bool ENT, bool MAG, bool HYP, bool UPW>
+__global__ void __launch_bounds__(256) rhs_update_v1(const UpdateArgs a) {
+  const int ix = blockIdx.x * blockDim.x + threadIdx.x + NG;
+  const int iy = blockIdx.y * blockDim.y + threadIdx.y + NG;
+  const int iz = blockIdx.z * blockDim.z + threadIdx.z + a.z_lo;
+  if (ix >= cP.nx + NG || iy >= cP.ny + NG || iz >= a.z_hi) return;
+  const long long o = ix + cP.sy * iy + cP.sz * iz;
+  GlobalTaps tp{a.fin + o};
+  constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
+  double rhs[NV];
+  rhs_cell<ENT, MAG, HYP, UPW>(tp, rhs);
+  const double dtb = (*a.dt_dev) * a.beta;
+  double force[3] = {0., 0., 0.};
+  if (a.frc.on) { // forcing.f90:2170-2345
+    const double2 fx = a.frc.fx[ix], fy = a.frc.fy[iy], fz = a.frc.fz[iz];
+    const double xr = fx.x * fy.x - fx.y * fy.y, xi = fx.x * fy.y + fx.y * fy.x;
+    const double re = xr * fz.x - xi * fz.y, im = xr * fz.y + xi * fz.x;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) force[j] = a.frc.fda[j] * (a.frc.coef1[j] * re - a.frc.coef2[j] * im);
+  }
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const long long q = o + k * cP.sv;
+    double d = rhs[k];
+    if (a.read_df) d = a.alpha * a.df[q] + d; // timestep.f90:113
+    if (a.write_df) a.df[q] = d;
+    double fn = tp.val(k) + dtb * d; // timestep.f90:160-161
+    if (k < 3) fn += force[k];
+    a.fout[q] = fn;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// periodic ghost zones (boundcond.f90:2387-2433), one launch per direction:
+// dir 0: x ghosts for interior (y,z); dir 1: y ghosts, all x, interior z; dir 2: z ghosts, all x,y
+// ---------------------------------------------------------------------------
+__global__ void ghost_fill(double *f, int dir, int nvar) {
+  const int mx = cP.mx, my = cP.my;
+  long long n0, n1; // extents of the two non-ghost dims of this pass
+  if (dir == 0) { n0 = cP.ny; n1 = cP.nz; }
+  else if (dir == 1) { n0 = mx; n1 = cP.nz; }
+  else { n0 = mx; n1 = my; }
+  const long long per_var = 2LL * NG * n0 * n1;
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (tid >= per_var * nvar) return;
+  const int k = (int)(tid / per_var);
+  long long r = tid % per_var;
+  long long src, dst;
+  if (dir == 0) {
+    const int g = (int)(r % (2 * NG)); r /= 2 * NG;
+    const int iy = (int)(r % n0) + NG, iz = (int)(r / n0) + NG;
+    const int gx = g < NG ? g : cP.nx + g; // ghost index
+    const int sx = g < NG ? g + cP.nx : g; // source: f(1:l1-1)=f(l2i:l2); f(l2+1:mx)=f(l1:l1i)
+    dst = gx + cP.sy * iy + cP.sz * iz;
+    src = sx + cP.sy * iy + cP.sz * iz;
+  } else if (dir == 1) {
+    const int ix = (int)(r % n0); r /= n0;
+    const int g = (int)(r % (2 * NG));
+    const int iz = (int)(r / (2 * NG)) + NG;
+    const int gy = g < NG ? g : cP.ny + g;
+    const int sy_ = g < NG ? g + cP.ny : g;
+    dst = ix + cP.sy * gy + cP.sz * iz;
+    src = ix + cP.sy * sy_ + cP.sz * iz;
+  } else {
+    const int ix = (int)(r % n0); r /= n0;
+    const int iy = (int)(r % n1);
+    const int g = (int)(r / n1);
+    const int gz = g < NG ? g : cP.nz + g;
+    const int sz_ = g < NG ? g + cP.nz : g;
+    dst = ix + cP.sy * iy + cP.sz * gz;
+    src = ix + cP.sy * iy + cP.sz * sz_;
+  }
+  f[dst + k * cP.sv] = f[src + k * cP.sv];
+}
+
+// ---------------------------------------------------------------------------
+// Courant pre-pass and diagnostics: per-block warp-shuffle reduction, per-block partials,
+// then a single-block fixed-order final reduction (bitwise reproducible).
+// ---------------------------------------------------------------------------
+constexpr int RED_THREADS = 256;
+
+template <bool ENT, bool MAG> __global__ void __launch_bounds__(RED_THREADS) cfl_kernel(const double *f, double *partial_max) {
+  __shared__ double sm[RED_THREADS / 32];
+  const long long ncell = (long long)cP.nx * cP.ny * cP.nz;
+  double m = 0.0;
+  for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncell; c += (long long)gridDim.x * blockDim.x) {
+    const int ix = (int)(c % cP.nx) + NG;
+    const long long r = c / cP.nx;
+    const int iy = (int)(r % cP.ny) + NG, iz = (int)(r / cP.ny) + NG;
+    GlobalTaps tp{f + ix + cP.sy * iy + cP.sz * iz};
+    m = fmax(m, cfl_cell<ENT, MAG>(tp).dt1);
+  }
+  m = warp_max(m);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    m = threadIdx.x < RED_THREADS / 32 ? sm[threadIdx.x] : 0.0;
+    m = warp_max(m);
+    if (threadIdx.x == 0) partial_max[blockIdx.x] = m;
+  }
+}
+
+// out[0] = max(dt1_init, partials)
+__global__ void final_max(const double *partial, int n, double *out) {
+  __shared__ double sm[32];
+  double m = cP.dt1_init;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) m = fmax(m, partial[i]);
+  m = warp_max(m);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    m = threadIdx.x < (blockDim.x >> 5) ? sm[threadIdx.x] : 0.0;
+    m = warp_max(m);
+    if (threadIdx.x == 0) out[0] = m;
+  }
+}
+
+// dt = 1/dt1 (set_dt sub.f90:4223-4254)
+__global__ void dt_from_dt1(const double *dt1, double *dt) { dt[0] = 1.0 / dt1[0]; }
+
+template <bool ENT, bool MAG>
+__global__ void __launch_bounds__(RED_THREADS) diag_kernel(const double *f, double *partial /*[grid][DS_NSUM+DM_NMAX]*/) {
+  __shared__ double sm[RED_THREADS / 32][DS_NSUM + DM_NMAX];
+  const long long ncell = (long long)cP.nx * cP.ny * cP.nz;
+  double s[DS_NSUM], m[DM_NMAX];
+#pragma unroll
+  for (int i = 0; i < DS_NSUM; ++i) s[i] = 0.0;
+#pragma unroll
+  for (int i = 0; i < DM_NMAX; ++i) m[i] = 0.0;
+  for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < ncell; c += (long long)gridDim.x * blockDim.x) {
+    const int ix = (int)(c % cP.nx) + NG;
+    const long long r = c / cP.nx;
+    const int iy = (int)(r % cP.ny) + NG, iz = (int)(r / cP.ny) + NG;
+    GlobalTaps tp{f + ix + cP.sy * iy + cP.sz * iz};
+    double cs[DS_NSUM], cm[DM_NMAX];
+    diag_cell<ENT, MAG>(tp, cs, cm);
+#pragma unroll
+    for (int i = 0; i < DS_NSUM; ++i) s[i] += cs[i];
+#pragma unroll
+    for (int i = 0; i < DM_NMAX; ++i) m[i] = fmax(m[i], cm[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < DS_NSUM; ++i) s[i] = warp_sum(s[i]);
+#pragma unroll
+  for (int i = 0; i < DM_NMAX; ++i) m[i] = warp_max(m[i]);
+  if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+    for (int i = 0; i < DS_NSUM; ++i) sm[threadIdx.x >> 5][i] = s[i];
+#pragma unroll
+    for (int i = 0; i < DM_NMAX; ++i) sm[threadIdx.x >> 5][DS_NSUM + i] = m[i];
+  }
+  __syncthreads();
+  if (threadIdx.x < DS_NSUM + DM_NMAX) {
+    double v = sm[0][threadIdx.x];
+    for (int w = 1; w < RED_THREADS / 32; ++w) v = threadIdx.x < DS_NSUM ? v + sm[w][threadIdx.x] : fmax(v, sm[w][threadIdx.x]);
+    partial[(long long)blockIdx.x * (DS_NSUM + DM_NMAX) + threadIdx.x] = v;
+  }
+}
+
+__global__ void diag_final(const double *partial, int nblocks, double *out /*[DS_NSUM+DM_NMAX]*/) {
+  const int q = threadIdx.x;
+  if (q >= DS_NSUM + DM_NMAX) return;
+  double v = 0.0;
+  for (int b = 0; b < nblocks; ++b) {
+    const double x = partial[(long long)b * (DS_NSUM + DM_NMAX) + q];
+    v = q < DS_NSUM ? v + x : fmax(v, x);
+  }
+  out[q] = v;
+}
+
+// ---------------------------------------------------------------------------
+// synthetic initial condition: ABC flow + Beltrami A + entropy wave + hashed noise
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double hash_noise(unsigned long long gx, unsigned long long gy, unsigned long long gz,
+                                             unsigned long long k, unsigned long long seed) {
+  // splitmix64 of a counter built from the GLOBAL cell index -> decomposition independent
+  unsigned long long z = seed + 0x9E3779B97F4A7C15ULL * (1ULL + gx + 4096ULL * (gy + 4096ULL * (gz + 4096ULL * k)));
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+  z = z ^ (z >> 31);
+  return (double)(z >> 11) * (1.0 / 9007199254740992.0); // U[0,1)
+}
+
+__global__ void init_synthetic_kernel(double *f, int ent, int mag, double x0, double y0, double z0, double dx, double dy,
+                                      double dz, int gx0, int gy0, int gz0, unsigned long long seed) {
+  const long long ncell = (long long)cP.nx * cP.ny * cP.nz;
+  const long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (c >= ncell) return;
+  const int i = (int)(c % cP.nx);
+  const long long r = c / cP.nx;
+  const int j = (int)(r % cP.ny), l = (int)(r / cP.ny);
+  const double x = x0 + i * dx, y = y0 + j * dy, z = z0 + l * dz;
+  const long long o = (i + NG) + cP.sy * (j + NG) + cP.sz * (l + NG);
+  double v[MAXVAR];
+  v[0] = 0.1 * (sin(z) + cos(y));
+  v[1] = 0.1 * (sin(x) + cos(z));
+  v[2] = 0.1 * (sin(y) + cos(x));
+  v[3] = 0.0;
+  int n = 4;
+  if (ent) v[n++] = 0.01 * sin(x) * cos(y);
+  if (mag) {
+    v[n++] = 0.01 * (sin(2 * z) + cos(2 * y));
+    v[n++] = 0.01 * (sin(2 * x) + cos(2 * z));
+    v[n++] = 0.01 * (sin(2 * y) + cos(2 * x));
+  }
+  for (int k = 0; k < n; ++k)
+    f[o + k * cP.sv] = v[k] + 1e-3 * (hash_noise(gx0 + i, gy0 + j, gz0 + l, k, seed) - 0.5);
+}
+
+// ---------------------------------------------------------------------------
+// NCCL, loaded lazily (only multi-GPU runs need it)
+// ---------------------------------------------------------------------------
+typedef struct ncclComm *ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+enum { ncclFloat64 = 8 };
+enum { ncclSum = 0, ncclMax = 2 };
+struct Nccl {
+  void *h = nullptr;
+  int (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  int (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  int (*CommDestroy)(ncclComm_t) = nullptr;
+  int (*Send)(const void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*Recv)(void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(int) = nullptr;
+  void load() {
+    if (h) return;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *n : names) {
+      h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+      if (h) break;
+    }
+    if (!h) die("cannot dlopen libnccl.so.2 (%s); multi-GPU runs need NCCL", dlerror());
+#define SYM(field, name)                                  \
+  *(void **)(&field) = dlsym(h, name);                    \
+  if (!field) die("NCCL symbol %s missing", name);
+    SYM(GetUniqueId, "ncclGetUniqueId");
+    SYM(CommInitRank, "ncclCommInitRank");
+    SYM(CommDestroy, "ncclCommDestroy");
+    SYM(Send, "ncclSend");
+    SYM(Recv, "ncclRecv");
+    SYM(AllReduce, "ncclAllReduce");
+    SYM(GroupStart, "ncclGroupStart");
+    SYM(GroupEnd, "ncclGroupEnd");
+    SYM(GetErrorString, "ncclGetErrorString");
+#undef SYM
+  }
+};
+static Nccl nccl;
+#define NCK(call)                                                                                   \
+  do {                                                                                              \
+    int r_ = (call);                                                                                \
+    if (r_ != 0) die("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, nccl.GetErrorString(r_)); \
+  } while (0)
+
+// ---------------------------------------------------------------------------
+// library state
+// ---------------------------------------------------------------------------
+struct State {
+  bool configured = false, initialized = false;
+  pcb200_config cfg{};
+  Pars P{};
+  size_t nreal = 0; // doubles per f buffer
+  double *f[2] = {nullptr, nullptr};
+  double *df = nullptr;
+  int cur = 0;
+  double *host_f = nullptr; // retained Fortran f (gpu_astaroth.cc:2040-2059)
+  cudaStream_t stream = nullptr, comm_stream = nullptr;
+  bool own_stream = false;
+  cudaEvent_t ev_ready = nullptr, ev_halo = nullptr;
+  // dt
+  double dt_host = 0.0;
+  int ldt = 0;
+  double *dt_dev = nullptr, *dt1_dev = nullptr;
+  double *pinned = nullptr; // small pinned scratch (32 doubles)
+  // reductions
+  double *partial = nullptr;
+  int red_blocks = 0;
+  double *diag_dev = nullptr;
+  bool diag_requested = false, diag_valid = false;
+  double reduced[PCB200_N_REDUCED] = {0};
+  // forcing
+  int lforce = 0;
+  double coef1[3], coef2[3], fda[3], kk[3], phase = 0, fact = 0, k1_ff = 1;
+  double2 *fx_dev = nullptr, *fy_dev = nullptr, *fz_dev = nullptr;
+  double2 *ftab_host = nullptr;
+  // nccl
+  ncclComm_t comm = nullptr;
+  int rank = 0, nranks = 1;
+  // bookkeeping
+  long long launches = 0;
+  bool timing = false;
+  std::vector<cudaEvent_t> ev_pool;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ev_pending;
+  double kernel_ms = 0.0;
+  long long kernel_launches = 0;
+};
+static State S;
+
+static void need_init(const char *who) {
+  if (!S.initialized) die("%s called before initialize_gpu_c", who);
+}
+
+static void derive_pars() {
+  const pcb200_config &c = S.cfg;
+  Pars &P = S.P;
+  P.nx = c.nx; P.ny = c.ny; P.nz = c.nz;
+  P.mx = c.nx + 2 * NG; P.my = c.ny + 2 * NG; P.mz = c.nz + 2 * NG;
+  P.nvar = c.nvar;
+  P.sy = P.mx; P.sz = (long long)P.mx * P.my; P.sv = P.sz * P.mz;
+  const double d[3] = {c.dx, c.dy, c.dz};
+  double d1[3];
+  for (int j = 0; j < 3; ++j) {
+    d1[j] = 1.0 / d[j];
+    P.dline_1[j] = d1[j];
+    P.d1fac[j] = (1.0 / 60.0) * d1[j];
+    P.d2fac[j] = d1[j] * d1[j];
+    P.d6fac[j] = std::pow(d1[j], 6);
+    P.d6upfac[j] = (1.0 / 60) * d1[j];
+    P.d5fac[j] = (1.0 / 2) * 1 / std::pow(d[j], 5);
+  }
+  P.dmfac[0] = (1. / 720.) * d1[0] * d1[1];
+  P.dmfac[1] = (1. / 720.) * d1[1] * d1[2];
+  P.dmfac[2] = (1. / 720.) * d1[2] * d1[0];
+  P.dxyz_2 = d1[0] * d1[0] + d1[1] * d1[1] + d1[2] * d1[2];
+  P.dxyz_4 = std::pow(d1[0], 4) + std::pow(d1[1], 4) + std::pow(d1[2], 4);
+  P.dxyz_6 = std::pow(d1[0], 6) + std::pow(d1[1], 6) + std::pow(d1[2], 6);
+  // eos_idealgas.f90:154-270
+  P.cs20 = c.cs20; P.gamma = c.gamma; P.gamma1 = 1 / c.gamma; P.gamma_m1 = c.gamma - 1.0;
+  P.cp = c.cp; P.cp1 = 1 / c.cp; P.cv1 = c.gamma * P.cp1; P.lnrho0 = c.lnrho0;
+  P.lnTT0 = (P.gamma_m1 != 0.0) ? std::log(c.cs20 / (c.cp * P.gamma_m1)) : std::log(c.cs20 / c.cp);
+  P.cp = 1 / P.cp1; // p%cp=1/cp1 (eos_idealgas.f90:811)
+  P.mu0 = c.mu0; P.mu01 = 1. / c.mu0;
+  P.nu = c.nu; P.nu_hyper3 = c.nu_hyper3; P.diffrho_hyper3 = c.diffrho_hyper3; P.chi = c.chi; P.eta = c.eta;
+  P.cdt = c.cdt; P.cdtv = c.cdtv; P.cdtv2 = c.cdtv2; P.cdtv3 = c.cdtv3;
+  P.dt1_init = (c.dtmax != 0.0) ? 1.0 / c.dtmax : 0.0;
+  P.lvisc_nu_const = c.lvisc_nu_const; P.lvisc_hyper3_simplified = c.lvisc_hyper3_simplified;
+  P.lvisc_hyper3_nu_const = c.lvisc_hyper3_nu_const; P.ldiff_hyper3lnrho = c.ldiff_hyper3lnrho;
+  P.lheatc_chiconst = c.lheatc_chiconst; P.lviscosity_heat = c.lviscosity_heat;
+  P.lresi_eta_const = c.lresi_eta_const; P.lohmic_heat = c.lohmic_heat; P.llorentzforce = c.llorentzforce;
+  P.lupw_uu = c.lupw_uu; P.lupw_lnrho = c.lupw_lnrho; P.lupw_ss = c.lupw_ss; P.lupw_aa = c.lupw_aa;
+}
+
+static void check_supported() {
+  const pcb200_config &c = S.cfg;
+  // the module refuses what it does not implement (gpu_astaroth.f90:211-228 convention)
+  if (c.nx < 1 || c.ny < 1 || c.nz < 1) die("bad grid %d %d %d", c.nx, c.ny, c.nz);
+  if (c.nx < NG || c.ny < NG || c.nz < NG) die("local grid smaller than nghost=3 is not supported");
+  if (c.nprocx != 1) die("nprocx must be 1 (z-slab / yz-pencil decomposition only)");
+  if (c.nprocy != 1) die("nprocy>1 (yz-pencils) not implemented yet; use z-slabs");
+  if (!(c.lperi[0] && c.lperi[1] && c.lperi[2])) die("only periodic boundary conditions ('p') are supported");
+  if (c.iux != 0 || c.ilnrho != 3) die("hydro (slots 1-3) and density (slot 4) are required in registration order");
+  const bool ent = c.iss >= 0, mag = c.iax >= 0;
+  if (ent && c.iss != 4) die("iss must be slot 5");
+  if (mag && c.iax != (ent ? 5 : 4)) die("iax must follow lnrho/ss");
+  const int nv = 4 + (ent ? 1 : 0) + (mag ? 3 : 0);
+  if (c.nvar != nv) die("nvar=%d does not match the module set (expected %d)", c.nvar, nv);
+  if (c.dx <= 0 || c.dy <= 0 || c.dz <= 0) die("non-positive grid spacing");
+  if (S.nranks != c.nprocy * c.nprocz) die("nprocy*nprocz=%d but %d NCCL ranks", c.nprocy * c.nprocz, S.nranks);
+}
+
+// ---------------------------------------------------------------------------
+// launch helpers
+// ---------------------------------------------------------------------------
+template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v1(const UpdateArgs &a, cudaStream_t st) {
+  dim3 b(64, 4, 1);
+  dim3 g((S.P.nx + b.x - 1) / b.x, (S.P.ny + b.y - 1) / b.y, (a.z_hi - a.z_lo + b.z - 1) / b.z);
+  rhs_update_v1<ENT, MAG, HYP, UPW><<<g, b, 0, st>>>(a);
+}
+
+static void launch_update(const UpdateArgs &a, cudaStream_t st) {
+  if (a.z_hi <= a.z_lo) return;
+  const bool ent = S.cfg.iss >= 0, mag = S.cfg.iax >= 0;
+  const bool hyp = S.cfg.lvisc_hyper3_simplified || S.cfg.lvisc_hyper3_nu_const || S.cfg.ldiff_hyper3lnrho;
+  const bool upw = S.cfg.lupw_uu || S.cfg.lupw_lnrho || S.cfg.lupw_ss || S.cfg.lupw_aa;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (S.timing) {
+    auto get = [&]() {
+      cudaEvent_t e;
+      if (!S.ev_pool.empty()) { e = S.ev_pool.back(); S.ev_pool.pop_back(); }
+      else CK(cudaEventCreate(&e));
+      return e;
+    };
+    e0 = get(); e1 = get();
+    CK(cudaEventRecord(e0, st));
+  }
+#define DISPATCH(E, M, H, U) launch_update_v1<E, M, H, U>(a, st)
+  const int key = (ent ? 8 : 0) | (mag ? 4 : 0) | (hyp ? 2 : 0) | (upw ? 1 : 0);
+  switch (key) {
+  case 0: DISPATCH(false, false, false, false); break;
+  case 1: DISPATCH(false, false, false, true); break;
+  case 2: DISPATCH(false, false, true, false); break;
+  case 3: DISPATCH(false, false, true, true); break;
+  case 4: DISPATCH(false, true, false, false); break;
+  case 5: DISPATCH(false, true, false, true); break;
+  case 6: DISPATCH(false, true, true, false); break;
+  case 7: DISPATCH(false, true, true, true); break;
+  case 8: DISPATCH(true, false, false, false); break;
+  case 9: DISPATCH(true, false, false, true); break;
+  case 10: DISPATCH(true, false, true, false); break;
+  case 11: DISPATCH(true, false, true, true); break;
+  case 12: DISPATCH(true, true, false, false); break;
+  case 13: DISPATCH(true, true, false, true); break;
+  case 14: DISPATCH(true, true, true, false); break;
+  default: DISPATCH(true, true, true, true); break;
+  }
+#undef DISPATCH
+  CK(cudaGetLastError());
+  S.launches++;
+  if (S.timing) {
+    CK(cudaEventRecord(e1, st));
+    S.ev_pending.emplace_back(e0, e1);
+    S.kernel_launches++;
+  }
+}
+
+static void launch_ghost(double *f, int dir, cudaStream_t st) {
+  const Pars &P = S.P;
+  long long n;
+  if (dir == 0) n = 2LL * NG * P.ny * P.nz;
+  else if (dir == 1) n = 2LL * NG * P.mx * P.nz;
+  else n = 2LL * NG * P.mx * P.my;
+  n *= P.nvar;
+  const int b = 256;
+  ghost_fill<<<(unsigned)((n + b - 1) / b), b, 0, st>>>(f, dir, P.nvar);
+  CK(cudaGetLastError());
+  S.launches++;
+}
+
+// z-slab halo exchange of 3 xy-planes per variable with the +-z neighbours
+// (replaces initiate/finalize_isendrcv_bdry, mpicomm.f90:1544-2271; z-slabs are contiguous
+// plane ranges of an x-fastest array, so no packing is needed)
+static void exchange_z(double *f, cudaStream_t st) {
+  const Pars &P = S.P;
+  const int up = (S.cfg.ipz + 1) % S.cfg.nprocz, dn = (S.cfg.ipz - 1 + S.cfg.nprocz) % S.cfg.nprocz;
+  const size_t cnt = (size_t)NG * P.sz;
+  NCK(nccl.GroupStart());
+  for (int k = 0; k < P.nvar; ++k) {
+    double *b = f + (size_t)k * P.sv;
+    // send top interior planes up, receive lower ghosts from below
+    NCK(nccl.Send(b + (size_t)P.nz * P.sz, cnt, ncclFloat64, up, S.comm, st));
+    NCK(nccl.Recv(b, cnt, ncclFloat64, dn, S.comm, st));
+    // send bottom interior planes down, receive upper ghosts from above
+    NCK(nccl.Send(b + (size_t)NG * P.sz, cnt, ncclFloat64, dn, S.comm, st));
+    NCK(nccl.Recv(b + (size_t)(NG + P.nz) * P.sz, cnt, ncclFloat64, up, S.comm, st));
+  }
+  NCK(nccl.GroupEnd());
+}
+
+// make all ghost zones of buffer f valid (x,y periodic wrap locally; z wrap or exchange)
+static void update_ghosts(double *f, cudaStream_t st) {
+  launch_ghost(f, 0, st);
+  launch_ghost(f, 1, st);
+  if (S.cfg.nprocz == 1) launch_ghost(f, 2, st);
+  else exchange_z(f, st);
+}
+
+template <bool ENT, bool MAG> static void launch_cfl_t(const double *f, cudaStream_t st) {
+  cfl_kernel<ENT, MAG><<<S.red_blocks, RED_THREADS, 0, st>>>(f, S.partial);
+}
+template <bool ENT, bool MAG> static void launch_diag_t(const double *f, cudaStream_t st) {
+  diag_kernel<ENT, MAG><<<S.red_blocks, RED_THREADS, 0, st>>>(f, S.partial);
+}
+
+// Courant dt of the step (equ.f90:408 -> sub.f90:4223): dt1 max over all cells and ranks
+static void compute_dt(cudaStream_t st) {
+  const bool ent = S.cfg.iss >= 0, mag = S.cfg.iax >= 0;
+  const double *f = S.f[S.cur];
+  if (ent && mag) launch_cfl_t<true, true>(f, st);
+  else if (ent) launch_cfl_t<true, false>(f, st);
+  else if (mag) launch_cfl_t<false, true>(f, st);
+  else launch_cfl_t<false, false>(f, st);
+  CK(cudaGetLastError());
+  final_max<<<1, 256, 0, st>>>(S.partial, S.red_blocks, S.dt1_dev);
+  CK(cudaGetLastError());
+  S.launches += 2;
+  if (S.nranks > 1) NCK(nccl.AllReduce(S.dt1_dev, S.dt1_dev, 1, ncclFloat64, ncclMax, S.comm, st));
+  dt_from_dt1<<<1, 1, 0, st>>>(S.dt1_dev, S.dt_dev);
+  CK(cudaGetLastError());
+  S.launches++;
+}
+
+static void compute_diagnostics(cudaStream_t st) {
+  const bool ent = S.cfg.iss >= 0, mag = S.cfg.iax >= 0;
+  const double *f = S.f[S.cur];
+  if (ent && mag) launch_diag_t<true, true>(f, st);
+  else if (ent) launch_diag_t<true, false>(f, st);
+  else if (mag) launch_diag_t<false, true>(f, st);
+  else launch_diag_t<false, false>(f, st);
+  CK(cudaGetLastError());
+  diag_final<<<1, 32, 0, st>>>(S.partial, S.red_blocks, S.diag_dev);
+  CK(cudaGetLastError());
+  S.launches += 2;
+  if (S.nranks > 1) {
+    NCK(nccl.GroupStart());
+    NCK(nccl.AllReduce(S.diag_dev, S.diag_dev, DS_NSUM, ncclFloat64, ncclSum, S.comm, st));
+    NCK(nccl.AllReduce(S.diag_dev + DS_NSUM, S.diag_dev + DS_NSUM, DM_NMAX, ncclFloat64, ncclMax, S.comm, st));
+    NCK(nccl.GroupEnd());
+  }
+  CK(cudaMemcpyAsync(S.pinned + 8, S.diag_dev, sizeof(double) * (DS_NSUM + DM_NMAX), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const double *s = S.pinned + 8, *m = S.pinned + 8 + DS_NSUM;
+  const double nw = (double)S.cfg.nx * S.cfg.ny * S.cfg.nz * S.cfg.nprocx * S.cfg.nprocy * S.cfg.nprocz; // nwgrid
+  double *r = S.reduced;
+  r[PCB200_RED_URMS] = std::sqrt(s[DS_U2] / nw);
+  r[PCB200_RED_UMAX] = std::sqrt(m[DM_U2]);
+  r[PCB200_RED_RHOM] = s[DS_RHO] / nw;
+  r[PCB200_RED_BRMS] = std::sqrt(s[DS_B2] / nw);
+  r[PCB200_RED_BMAX] = std::sqrt(m[DM_B2]);
+  r[PCB200_RED_JRMS] = std::sqrt(s[DS_J2] / nw);
+  r[PCB200_RED_JMAX] = std::sqrt(m[DM_J2]);
+  r[PCB200_RED_ABM] = s[DS_AB] / nw;
+  r[PCB200_RED_JBM] = s[DS_JB] / nw;
+  r[PCB200_RED_OUM] = s[DS_OU] / nw;
+  r[PCB200_RED_EPSK] = s[DS_EPSK] / nw;
+  r[PCB200_RED_SSM] = s[DS_SS] / nw;
+  r[PCB200_RED_DTU] = m[DM_DTU];
+  r[PCB200_RED_DTC] = m[DM_DTC];
+  r[PCB200_RED_DTB] = m[DM_DTB];
+  r[PCB200_RED_DTNU] = m[DM_DTNU];
+  S.diag_valid = true;
+}
+
+static void upload_forcing_tables(cudaStream_t st) {
+  // fxyz_coefs_hel forcing.f90:2003-2064: fx=exp(i(kx*k1_ff*x+phase))*fact, fy=exp(i ky k1_ff y), fz likewise
+  const Pars &P = S.P;
+  double2 *hx = S.ftab_host, *hy = hx + P.mx, *hz = hy + P.my;
+  for (int i = 0; i < P.mx; ++i) {
+    const double x = S.cfg.x0 + (i - NG) * S.cfg.dx;
+    const double arg = S.kk[0] * S.k1_ff * x + S.phase;
+    hx[i] = make_double2(std::cos(arg) * S.fact, std::sin(arg) * S.fact);
+  }
+  for (int i = 0; i < P.my; ++i) {
+    const double y = S.cfg.y0 + (i - NG) * S.cfg.dy;
+    const double arg = S.kk[1] * S.k1_ff * y;
+    hy[i] = make_double2(std::cos(arg), std::sin(arg));
+  }
+  for (int i = 0; i < P.mz; ++i) {
+    const double z = S.cfg.z0 + (i - NG) * S.cfg.dz;
+    const double arg = S.kk[2] * S.k1_ff * z;
+    hz[i] = make_double2(std::cos(arg), std::sin(arg));
+  }
+  CK(cudaMemcpyAsync(S.fx_dev, hx, sizeof(double2) * (P.mx + P.my + P.mz), cudaMemcpyHostToDevice, st));
+}
+
+static void drain_timing() {
+  for (auto &p : S.ev_pending) {
+    float ms = 0.f;
+    CK(cudaEventSynchronize(p.second));
+    CK(cudaEventElapsedTime(&ms, p.first, p.second));
+    S.kernel_ms += ms;
+    S.ev_pool.push_back(p.first);
+    S.ev_pool.push_back(p.second);
+  }
+  S.ev_pending.clear();
+}
+
+} // namespace pcb200
+
+using namespace pcb200;
+
+// every entry point is exported plain and with a trailing underscore (FTNIZE, headers_c.h:31-37)
+#define FTN_ALIAS(name) extern "C" __attribute__((alias(#name))) void name##_();
+
+// ===========================================================================
+// Part 2: configuration
+// ===========================================================================
+extern "C" int pcb200_sizeof_config(void) { return (int)sizeof(pcb200_config); }
+
+extern "C" void pcb200_configure(const pcb200_config *cfg) {
+  if (S.initialized) die("pcb200_configure called while initialized; call finalize_gpu_c first");
+  S.cfg = *cfg;
+  S.configured = true;
+}
+
+extern "C" void pcb200_set_dt(const double *dt, const int *ldt) {
+  S.dt_host = *dt;
+  S.ldt = *ldt;
+  if (S.initialized && !S.ldt) {
+    S.pinned[0] = S.dt_host;
+    CK(cudaMemcpyAsync(S.dt_dev, S.pinned, sizeof(double), cudaMemcpyHostToDevice, S.stream));
+    CK(cudaStreamSynchronize(S.stream)); // pinned[0] may be rewritten by the next call
+  }
+}
+extern "C" void pcb200_get_dt1_max(double *dt1_max) {
+  need_init("pcb200_get_dt1_max");
+  CK(cudaMemcpyAsync(S.pinned + 1, S.dt1_dev, sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CK(cudaStreamSynchronize(S.stream));
+  *dt1_max = S.pinned[1];
+}
+extern "C" void pcb200_get_dt(double *dt) {
+  need_init("pcb200_get_dt");
+  CK(cudaMemcpyAsync(S.pinned + 2, S.dt_dev, sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CK(cudaStreamSynchronize(S.stream));
+  *dt = S.pinned[2];
+  S.dt_host = *dt;
+}
+
+extern "C" void pcb200_set_forcing_hel(const int *lforce, const double coef1[3], const double coef2[3], const double fda[3],
+                                       const double kk[3], const double *phase, const double *fact, const double *k1_ff) {
+  S.lforce = *lforce;
+  if (!S.lforce) return;
+  for (int j = 0; j < 3; ++j) { S.coef1[j] = coef1[j]; S.coef2[j] = coef2[j]; S.fda[j] = fda[j]; S.kk[j] = kk[j]; }
+  S.phase = *phase; S.fact = *fact; S.k1_ff = *k1_ff;
+}
+
+extern "C" void pcb200_request_diagnostics(void) { S.diag_requested = true; }
+
+extern "C" void pcb200_nccl_get_unique_id(char id[128]) {
+  nccl.load();
+  ncclUniqueId u;
+  NCK(nccl.GetUniqueId(&u));
+  std::memcpy(id, u.internal, 128);
+}
+
+static void select_device() {
+  int ndev = 0;
+  CK(cudaGetDeviceCount(&ndev));
+  if (ndev < 1) die("no CUDA device visible; this module has no CPU fallback");
+  int dev = S.cfg.device;
+  if (dev < 0) {
+    const char *lr = std::getenv("LOCAL_RANK");
+    dev = lr ? std::atoi(lr) % ndev : S.rank % ndev;
+  }
+  CK(cudaSetDevice(dev));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major != 10) die("device %d is sm_%d%d; this library is built for sm_100a (B200) only", dev, prop.major, prop.minor);
+}
+
+extern "C" void pcb200_nccl_init(const char id[128], const int *rank, const int *nranks) {
+  if (!S.configured) die("pcb200_nccl_init: call pcb200_configure first");
+  S.rank = *rank;
+  S.nranks = *nranks;
+  if (S.nranks <= 1) return;
+  nccl.load();
+  select_device();
+  ncclUniqueId u;
+  std::memcpy(u.internal, id, 128);
+  NCK(nccl.CommInitRank(&S.comm, S.nranks, u, S.rank));
+}
+
+extern "C" void pcb200_set_stream(void *cuda_stream) {
+  if (S.initialized) CK(cudaStreamSynchronize(S.stream));
+  if (S.own_stream && S.stream) { CK(cudaStreamDestroy(S.stream)); S.own_stream = false; }
+  if (cuda_stream) S.stream = (cudaStream_t)cuda_stream;
+  else { CK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking)); S.own_stream = true; }
+}
+
+extern "C" void pcb200_synchronize(void) {
+  need_init("pcb200_synchronize");
+  CK(cudaStreamSynchronize(S.stream));
+  CK(cudaStreamSynchronize(S.comm_stream));
+}
+
+extern "C" long long pcb200_launch_count(void) { return S.launches; }
+
+extern "C" void pcb200_enable_kernel_timing(const int *on) { S.timing = (*on != 0); }
+extern "C" void pcb200_kernel_timing(double *ms, long long *launches, const int *reset) {
+  drain_timing();
+  *ms = S.kernel_ms;
+  *launches = S.kernel_launches;
+  if (*reset) { S.kernel_ms = 0.0; S.kernel_launches = 0; }
+}
+
+extern "C" void pcb200_init_synthetic(const int *seed) {
+  need_init("pcb200_init_synthetic");
+  const Pars &P = S.P;
+  const long long n = (long long)P.nx * P.ny * P.nz;
+  init_synthetic_kernel<<<(unsigned)((n + 255) / 256), 256, 0, S.stream>>>(
+      S.f[S.cur], S.cfg.iss >= 0, S.cfg.iax >= 0, S.cfg.x0, S.cfg.y0, S.cfg.z0, S.cfg.dx, S.cfg.dy, S.cfg.dz,
+      S.cfg.ipx * S.cfg.nx, S.cfg.ipy * S.cfg.ny, S.cfg.ipz * S.cfg.nz, (unsigned long long)*seed);
+  CK(cudaGetLastError());
+  S.launches++;
+  update_ghosts(S.f[S.cur], S.stream);
+}
+
+// ===========================================================================
+// Part 1: reference GPU-module interface
+// ===========================================================================
+extern "C" void register_gpu_c(void) {}
+FTN_ALIAS(register_gpu_c)
+
+extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, int *lread_all, int *lcpu_dt, int *lsparse) {
+  (void)comm_fint; (void)t; (void)nt; (void)lread_all; (void)lcpu_dt; (void)lsparse;
+  if (!S.configured) die("initialize_gpu_c: pcb200_configure must be called first (sizes/parameters)");
+  if (S.initialized) die("initialize_gpu_c called twice");
+  check_supported();
+  select_device();
+  derive_pars();
+  const Pars &P = S.P;
+  S.host_f = f;
+  S.nreal = (size_t)P.sv * P.nvar;
+  if (!S.stream) { CK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking)); S.own_stream = true; }
+  CK(cudaStreamCreateWithFlags(&S.comm_stream, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&S.ev_ready, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&S.ev_halo, cudaEventDisableTiming));
+  CK(cudaMalloc(&S.f[0], S.nreal * sizeof(double)));
+  CK(cudaMalloc(&S.f[1], S.nreal * sizeof(double)));
+  CK(cudaMalloc(&S.df, S.nreal * sizeof(double)));
+  CK(cudaMemsetAsync(S.f[0], 0, S.nreal * sizeof(double), S.stream));
+  CK(cudaMemsetAsync(S.f[1], 0, S.nreal * sizeof(double), S.stream));
+  CK(cudaMemsetAsync(S.df, 0, S.nreal * sizeof(double), S.stream));
+  S.cur = 0;
+  CK(cudaMalloc(&S.dt_dev, sizeof(double)));
+  CK(cudaMalloc(&S.dt1_dev, sizeof(double)));
+  CK(cudaMallocHost(&S.pinned, 64 * sizeof(double)));
+  int nsm = 148;
+  CK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, 0));
+  S.red_blocks = nsm * 8;
+  CK(cudaMalloc(&S.partial, sizeof(double) * S.red_blocks * (DS_NSUM + DM_NMAX)));
+  CK(cudaMalloc(&S.diag_dev, sizeof(double) * (DS_NSUM + DM_NMAX)));
+  CK(cudaMalloc(&S.fx_dev, sizeof(double2) * (P.mx + P.my + P.mz)));
+  S.fy_dev = S.fx_dev + P.mx;
+  S.fz_dev = S.fy_dev + P.my;
+  CK(cudaMallocHost(&S.ftab_host, sizeof(double2) * (P.mx + P.my + P.mz)));
+  CK(cudaMemcpyToSymbolAsync(cP, &S.P, sizeof(Pars), 0, cudaMemcpyHostToDevice, S.stream));
+  S.pinned[0] = S.dt_host;
+  CK(cudaMemcpyAsync(S.dt_dev, S.pinned, sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  CK(cudaStreamSynchronize(S.stream));
+  S.initialized = true;
+}
+FTN_ALIAS(initialize_gpu_c)
+
+extern "C" void finalize_gpu_c(void) {
+  if (!S.initialized) return;
+  CK(cudaDeviceSynchronize());
+  drain_timing();
+  for (cudaEvent_t e : S.ev_pool) cudaEventDestroy(e);
+  S.ev_pool.clear();
+  cudaFree(S.f[0]); cudaFree(S.f[1]); cudaFree(S.df);
+  cudaFree(S.dt_dev); cudaFree(S.dt1_dev); cudaFree(S.partial); cudaFree(S.diag_dev); cudaFree(S.fx_dev);
+  cudaFreeHost(S.pinned); cudaFreeHost(S.ftab_host);
+  cudaEventDestroy(S.ev_ready); cudaEventDestroy(S.ev_halo);
+  cudaStreamDestroy(S.comm_stream);
+  if (S.own_stream) cudaStreamDestroy(S.stream);
+  if (S.comm) { nccl.CommDestroy(S.comm); }
+  const long long l = S.launches;
+  S = State();
+  S.launches = l;
+}
+FTN_ALIAS(finalize_gpu_c)
+
+extern "C" void load_farray_c(void) {
+  need_init("load_farray_c");
+  if (!S.host_f) die("load_farray_c: no host f-array was retained by initialize_gpu_c");
+  CK(cudaMemcpyAsync(S.f[S.cur], S.host_f, S.nreal * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  update_ghosts(S.f[S.cur], S.stream);
+  CK(cudaStreamSynchronize(S.stream));
+}
+FTN_ALIAS(load_farray_c)
+
+extern "C" void copy_farray_c(double *f) {
+  need_init("copy_farray_c");
+  CK(cudaMemcpyAsync(f, S.f[S.cur], S.nreal * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  CK(cudaStreamSynchronize(S.stream));
+}
+FTN_ALIAS(copy_farray_c)
+
+extern "C" void get_farray_ptr_gpu_c(double **p_in, double **p_out) {
+  need_init("get_farray_ptr_gpu_c");
+  *p_in = S.f[S.cur];
+  *p_out = S.f[S.cur ^ 1];
+}
+FTN_ALIAS(get_farray_ptr_gpu_c)
+
+extern "C" void before_boundary_gpu_c(int *lrmv, int *isubstep, double *t, int *lsubstepping) {
+  (void)lrmv; (void)isubstep; (void)t; (void)lsubstepping; // nothing to do for the supported physics
+}
+FTN_ALIAS(before_boundary_gpu_c)
+extern "C" void update_after_substep_gpu_c(void) {}
+FTN_ALIAS(update_after_substep_gpu_c)
+extern "C" void split_update_gpu_c(double *f) { (void)f; }
+FTN_ALIAS(split_update_gpu_c)
+extern "C" void radtransfer_gpu_c(void) { die("radtransfer_gpu: radiation is not supported by gpu_b200"); }
+FTN_ALIAS(radtransfer_gpu_c)
+extern "C" void reload_gpu_config_c(void) {
+  need_init("reload_gpu_config_c");
+  derive_pars();
+  CK(cudaStreamSynchronize(S.stream));
+  CK(cudaMemcpyToSymbol(cP, &S.P, sizeof(Pars)));
+}
+FTN_ALIAS(reload_gpu_config_c)
+
+// The first dt of a Courant run is computed inside substep 1 (exact CPU semantics), so nothing
+// has to be prepared here (gpu_astaroth.cc needs this only for its lagged dt).
+extern "C" void gpu_prepare_for_first_substep_c(double *t) { (void)t; }
+FTN_ALIAS(gpu_prepare_for_first_substep_c)
+
+extern "C" void rhs_gpu_c(int *isubstep, double *t) {
+  (void)t;
+  need_init("rhs_gpu_c");
+  static const double alpha_ts[3] = {0.0, -5.0 / 9.0, -153.0 / 128.0}; // timestep.f90:39-44
+  static const double beta_ts[3] = {1.0 / 3.0, 15.0 / 16.0, 8.0 / 15.0};
+  const int it = *isubstep;
+  if (it < 1 || it > 3) die("rhs_gpu_c: isubstep=%d (itorder=3 only)", it);
+  cudaStream_t st = S.stream;
+  if (it == 1) {
+    if (S.diag_requested) { compute_diagnostics(st); S.diag_requested = false; }
+    if (S.ldt) compute_dt(st); // lupdate_courant_dt (equ.f90:106)
+  }
+  UpdateArgs a;
+  a.fin = S.f[S.cur];
+  a.fout = S.f[S.cur ^ 1];
+  a.df = S.df;
+  a.dt_dev = S.dt_dev;
+  a.alpha = alpha_ts[it - 1];
+  a.beta = beta_ts[it - 1];
+  a.read_df = it > 1;
+  a.write_df = it < 3;
+  a.frc.on = 0;
+  if (it == 3 && S.lforce) {
+    upload_forcing_tables(st);
+    a.frc.on = 1;
+    for (int j = 0; j < 3; ++j) { a.frc.coef1[j] = S.coef1[j]; a.frc.coef2[j] = S.coef2[j]; a.frc.fda[j] = S.fda[j]; }
+    a.frc.fx = S.fx_dev; a.frc.fy = S.fy_dev; a.frc.fz = S.fz_dev;
+  }
+  a.z_lo = NG;
+  a.z_hi = NG + S.P.nz;
+  launch_update(a, st);
+  S.cur ^= 1;
+  update_ghosts(S.f[S.cur], st);
+  if (it == 1 && S.ldt) { // the host driver needs dt for t+=dtsub (timestep.f90:150-152,201)
+    double d;
+    pcb200_get_dt(&d);
+    S.reduced[PCB200_RED_DT] = d;
+    CK(cudaMemcpyAsync(S.pinned + 1, S.dt1_dev, sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    S.reduced[PCB200_RED_DT1MAX] = S.pinned[1];
+  } else if (it == 1) {
+    S.reduced[PCB200_RED_DT] = S.dt_host;
+  }
+}
+FTN_ALIAS(rhs_gpu_c)
+
+extern "C" void get_gpu_reduced_vars_c(double *dst) {
+  need_init("get_gpu_reduced_vars_c");
+  for (int i = 0; i < PCB200_N_REDUCED; ++i) dst[i] = S.reduced[i];
+}
+FTN_ALIAS(get_gpu_reduced_vars_c)
+
+extern "C" void test_bcs_c(void) { need_init("test_bcs_c"); }
+FTN_ALIAS(test_bcs_c)
+
+// updateInConfig* (gpu_astaroth.cc:2179-2241): run-time parameter pushes by name
+static const char *scal_names[] = {"nu", "eta", "chi", "nu_hyper3", "diffrho_hyper3", "cs20", "cdt", "cdtv", "cdtv3", nullptr};
+static double *scal_ptr(int i) {
+  switch (i) {
+  case 0: return &S.cfg.nu; case 1: return &S.cfg.eta; case 2: return &S.cfg.chi; case 3: return &S.cfg.nu_hyper3;
+  case 4: return &S.cfg.diffrho_hyper3; case 5: return &S.cfg.cs20; case 6: return &S.cfg.cdt; case 7: return &S.cfg.cdtv;
+  case 8: return &S.cfg.cdtv3; default: return nullptr;
+  }
+}
+extern "C" void update_on_gpu_scal_by_ind_c(int *index, double *value) {
+  double *p = scal_ptr(*index);
+  if (!p) die("update_on_gpu_scal_by_ind_c: bad index %d", *index);
+  *p = *value;
+  if (S.initialized) reload_gpu_config_c();
+}
+extern "C" __attribute__((alias("update_on_gpu_scal_by_ind_c"))) void update_on_gpu_scal_by_ind_c_(int *, double *);
+extern "C" int update_on_gpu_scal_by_name_c(const char *name, double *value) {
+  for (int i = 0; scal_names[i]; ++i)
+    if (std::strcmp(name, scal_names[i]) == 0) {
+      int idx = i;
+      update_on_gpu_scal_by_ind_c(&idx, value);
+      return i;
+    }
+  return -1;
+}
+extern "C" __attribute__((alias("update_on_gpu_scal_by_name_c"))) int update_on_gpu_scal_by_name_c_(const char *, double *);
+extern "C" int update_on_gpu_vec_by_name_c(const char *name, double *value) { (void)name; (void)value; return -1; }
+extern "C" __attribute__((alias("update_on_gpu_vec_by_name_c"))) int update_on_gpu_vec_by_name_c_(const char *, double *);
+extern "C" int update_on_gpu_arr_by_name_c(const char *name) { (void)name; return -1; }
+extern "C" __attribute__((alias("update_on_gpu_arr_by_name_c"))) int update_on_gpu_arr_by_name_c_(const char *);
+extern "C" void update_on_gpu_vec_by_ind_c(int *index, double *value) { (void)value; die("update_on_gpu_vec_by_ind_c: bad index %d", *index); }
+extern "C" __attribute__((alias("update_on_gpu_vec_by_ind_c"))) void update_on_gpu_vec_by_ind_c_(int *, double *);
+extern "C" void update_on_gpu_arr_by_ind_c(int *index) { die("update_on_gpu_arr_by_ind_c: bad index %d", *index); }
+extern "C" __attribute__((alias("update_on_gpu_arr_by_ind_c"))) void update_on_gpu_arr_by_ind_c_(int *);
+// gpu_astaroth_ansi.c pos_real_ptr_c: address of variable slot `ind` inside a device f-array
+extern "C" void *pos_real_ptr_c(void **ptr, int *ind) {
+  need_init("pos_real_ptr_c");
+  return (void *)((double *)(*ptr) + (size_t)(*ind) * S.P.sv);
+}
+extern "C" __attribute__((alias("pos_real_ptr_c"))) void *pos_real_ptr_c_(void **, int *);

@@ -1,0 +1,94 @@
+/*                             gpu_b200_ansi.c
+                              ----------------
+   C shim compiled inside Pencil Code's src/ (GPU_INTERFACE object for GPU=gpu_b200; the role
+   gpu_astaroth_ansi.c plays for Astaroth).  It fetches the physics parameters that are private
+   to their Fortran modules through the existing pushpars2c address tables and forwards the
+   helical-forcing coefficients, then everything goes to libpcb200.so (include/pcb200.h).
+
+   Table indices (1-based in Fortran, so -1 here) are those of the reference:
+     viscosity.f90:3250-3255,3311   nu(1) nu_hyper3(3) lvisc_nu_const(5) lvisc_hyper3_nu_const(6)
+                                    lvisc_hyper3_simplified(62)
+     magnetic.f90:12063-12070,12166 eta(1) lresi_eta_const(4) lupw_aa(7) llorentzforce(8) lohmic_heat(105)
+     eos_idealgas.f90:4589-4594     cs20(1) gamma(2) cp(4) lnrho0(5)
+     density.f90:4591-4593          ldiff_hyper3lnrho(3) diffrho_hyper3(4) lupw_lnrho(5)
+     hydro.f90:9367                 lupw_uu(2)
+     entropy.f90:8675-8816          chi(1) lheatc_chiconst(18) lupw_ss(29) lviscosity_heat(141)
+   Module-procedure symbol names follow the compiler's mangling; the Makefile passes
+   MODULE_PREFIX/INFIX/SUFFIX exactly as it does for the Astaroth glue (gfortran: __ , _MOD_ , "").
+*/
+#include <stddef.h>
+#include "headers_c.h"
+#include "pcb200.h"
+
+#ifndef MODULE_PREFIX
+#define MODULE_PREFIX __
+#define MODULE_INFIX _MOD_
+#define MODULE_SUFFIX
+#endif
+#define PC_CAT5_(a, b, c, d, e) a##b##c##d##e
+#define PC_CAT5(a, b, c, d, e) PC_CAT5_(a, b, c, d, e)
+#define MODPROC(mod, proc) PC_CAT5(MODULE_PREFIX, mod, MODULE_INFIX, proc, MODULE_SUFFIX)
+
+#define NPAR_MAX 2048
+extern void MODPROC(viscosity, pushpars2c)(FINT8 *);
+extern void MODPROC(magnetic, pushpars2c)(FINT8 *);
+extern void MODPROC(equationofstate, pushpars2c)(FINT8 *);
+extern void MODPROC(density, pushpars2c)(FINT8 *);
+extern void MODPROC(hydro, pushpars2c)(FINT8 *);
+extern void MODPROC(energy, pushpars2c)(FINT8 *);
+extern void MODPROC(forcing, forcing_pars_hel)(REAL *coef1, REAL *coef2, REAL *coef3, REAL *fda, REAL *kk,
+                                               REAL *phase, REAL *fact);
+extern void MODPROC(forcing, pushpars2c)(FINT8 *);
+
+#define PD(tab, i) (*(double *)(tab)[(i)-1])
+#define PI_(tab, i) (*(int *)(tab)[(i)-1])
+
+void pcb200_fill_physics_pars_c(pcb200_config *c)
+{
+  static FINT8 p[NPAR_MAX];
+  int i;
+
+  for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+  MODPROC(equationofstate, pushpars2c)(p);
+  c->cs20 = PD(p, 1); c->gamma = PD(p, 2); c->cp = PD(p, 4); c->lnrho0 = PD(p, 5);
+
+  for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+  MODPROC(viscosity, pushpars2c)(p);
+  c->nu = PD(p, 1); c->nu_hyper3 = PD(p, 3);
+  c->lvisc_nu_const = PI_(p, 5); c->lvisc_hyper3_nu_const = PI_(p, 6); c->lvisc_hyper3_simplified = PI_(p, 62);
+
+  for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+  MODPROC(density, pushpars2c)(p);
+  c->ldiff_hyper3lnrho = PI_(p, 3); c->diffrho_hyper3 = PD(p, 4); c->lupw_lnrho = PI_(p, 5);
+
+  for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+  MODPROC(hydro, pushpars2c)(p);
+  c->lupw_uu = PI_(p, 2);
+
+  c->chi = 0.; c->lheatc_chiconst = 0; c->lupw_ss = 0; c->lviscosity_heat = 1;
+  if (c->iss >= 0) {
+    for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+    MODPROC(energy, pushpars2c)(p);
+    c->chi = PD(p, 1); c->lheatc_chiconst = PI_(p, 18); c->lupw_ss = PI_(p, 29); c->lviscosity_heat = PI_(p, 141);
+  }
+  c->eta = 0.; c->lresi_eta_const = 0; c->lupw_aa = 0; c->llorentzforce = 1; c->lohmic_heat = 1;
+  if (c->iax >= 0) {
+    for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+    MODPROC(magnetic, pushpars2c)(p);
+    c->eta = PD(p, 1); c->lresi_eta_const = PI_(p, 4); c->lupw_aa = PI_(p, 7); c->llorentzforce = PI_(p, 8);
+    c->lohmic_heat = PI_(p, 105);
+  }
+}
+
+/* called by rhs_GPU before the last substep: draw the step's coefficients with the host RNG
+   (forcing.f90:1731-1746 forcing_pars_hel) and hand them to the device */
+void pcb200_push_forcing_c(void)
+{
+  static FINT8 p[NPAR_MAX];
+  REAL coef1[3], coef2[3], coef3[3], fda[3], kk[3], phase, fact, k1_ff;
+  int on = 1;
+  MODPROC(forcing, forcing_pars_hel)(coef1, coef2, coef3, fda, kk, &phase, &fact);
+  MODPROC(forcing, pushpars2c)(p);
+  k1_ff = PD(p, 1); /* forcing.f90:6620 */
+  pcb200_set_forcing_hel(&on, coef1, coef2, fda, kk, &phase, &fact, &k1_ff);
+}

@@ -1,0 +1,143 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI with host buffers, against the
+CPU oracle on identical seeded inputs.  Tolerances are those of BASELINE.json's north_star:
+f-array after 1 substep <= 1e-12 relative L-inf, after 100 steps <= 1e-9, time series likewise."""
+import numpy as np
+import pytest
+
+from pencil_code_b200 import config as pcfg
+from pencil_code_b200 import synthetic
+
+import parity_util as pu
+
+pytestmark = pytest.mark.gpu
+
+TOL_SUBSTEP = 1e-12
+TOL_100 = 1e-9
+
+CASES = {
+    "iso_mhd": dict(n=32, entropy=False, magnetic=True, nu=5e-3, eta=5e-3),
+    "mhd_entropy": dict(n=32, entropy=True, magnetic=True, nu=5e-3, eta=5e-3, chi=5e-3),
+    "hydro_entropy": dict(n=24, entropy=True, magnetic=False, nu=5e-3, chi=2e-3),
+    "hydro_hyper3": dict(n=32, entropy=False, magnetic=False, hyper3=True),
+    "mhd_entropy_upwind": dict(n=24, entropy=True, magnetic=True, nu=5e-3, eta=5e-3, chi=5e-3, upwind=True),
+    "ragged": dict(n=37, ny=19, nz=11, entropy=True, magnetic=True, nu=4e-3, eta=3e-3, chi=2e-3),
+}
+
+
+def _cfg(name, **over):
+    kw = dict(CASES[name])
+    n = kw.pop("n")
+    ent, mag = kw.pop("entropy"), kw.pop("magnetic")
+    c = pcfg.make_config(n, ent, mag, cdt=0.4, cdtv=0.3, **kw)
+    c.update(over)
+    return c
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_one_substep(oracle_mod, name):
+    cfg = _cfg(name)
+    fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 0, dt=pcfg.fixed_dt(cfg), substeps_only=1)
+    err = pu.rel_linf(fg, fc)
+    assert err.max() <= TOL_SUBSTEP, (name, err)
+
+
+@pytest.mark.parametrize("name", ["iso_mhd", "mhd_entropy", "ragged"])
+def test_three_substeps_and_ghosts(oracle_mod, name):
+    cfg = _cfg(name)
+    fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 0, dt=pcfg.fixed_dt(cfg), substeps_only=3)
+    err = pu.rel_linf(fg, fc)
+    assert err.max() <= 5e-12, (name, err)
+    # copy_farray_from_GPU returns valid periodic ghost zones (incl. edges and corners)
+    g = fg.copy()
+    nz, ny, nx = (s - 6 for s in g.shape[1:])
+    g[..., :3] = g[..., nx:nx + 3]; g[..., nx + 3:] = g[..., 3:6]
+    g[..., :3, :] = g[..., ny:ny + 3, :]; g[..., ny + 3:, :] = g[..., 3:6, :]
+    g[..., :3, :, :] = g[..., nz:nz + 3, :, :]; g[..., nz + 3:, :, :] = g[..., 3:6, :, :]
+    assert np.array_equal(g, fg)
+
+
+def test_nonisotropic_grid_spacing(oracle_mod):
+    cfg = _cfg("mhd_entropy")
+    cfg.update(dx=0.21, dy=0.17, dz=0.26)
+    fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 0, dt=0.01, substeps_only=2)
+    assert pu.rel_linf(fg, fc).max() <= 2e-12
+
+
+@pytest.mark.parametrize("name", ["iso_mhd", "mhd_entropy"])
+def test_100_steps_fixed_dt_with_time_series(oracle_mod, name):
+    cfg = _cfg(name)
+    fg, fc, sg, sc, (dtg, dtc, tg, tc) = pu.run_both(cfg, oracle_mod, 100, dt=pcfg.fixed_dt(cfg), diag_every=10)
+    err = pu.rel_linf(fg, fc)
+    assert err.max() <= TOL_100, (name, err)
+    assert abs(tg - tc) <= 1e-12 * abs(tc)
+    keys = ["urms", "umax", "rhom", "dt"] + (["brms", "bmax", "jrms", "abm", "jbm"] if cfg["iax"] >= 0 else [])
+    for a, b in zip(sg, sc):
+        for k in keys:
+            assert abs(a[k] - b[k]) <= TOL_100 * max(abs(b[k]), 1e-300), (k, a[k], b[k])
+
+
+def test_100_steps_courant_dt(oracle_mod):
+    """ldt=T: dt comes from the CFL reduction inside substep 1 of every step (equ.f90:408)."""
+    cfg = _cfg("mhd_entropy")
+    fg, fc, sg, sc, (dtg, dtc, tg, tc) = pu.run_both(cfg, oracle_mod, 100, dt=0.0, ldt=True, diag_every=20)
+    assert abs(dtg - dtc) <= 1e-12 * dtc
+    assert abs(tg - tc) <= 1e-10 * tc
+    assert pu.rel_linf(fg, fc).max() <= TOL_100
+    for a, b in zip(sg, sc):
+        for k in ("urms", "brms", "dt", "dtu", "dtc", "dtb", "dtnu", "epsK", "oum"):
+            assert abs(a[k] - b[k]) <= TOL_100 * max(abs(b[k]), 1e-300), (k, a[k], b[k])
+
+
+def test_helical_forcing_30_steps(oracle_mod):
+    cfg = _cfg("iso_mhd")
+    kv = pcfg.kvectors()
+    fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 30, dt=pcfg.fixed_dt(cfg), forcing=kv)
+    assert pu.rel_linf(fg, fc).max() <= TOL_100
+    # the forcing did something: compare with an unforced run
+    fg0, _, _, _, _ = pu.run_both(cfg, oracle_mod, 30, dt=pcfg.fixed_dt(cfg))
+    assert np.abs(pu.interior(fg)[:3] - pu.interior(fg0)[:3]).max() > 1e-4
+
+
+def test_hyper3_20_steps(oracle_mod):
+    cfg = _cfg("hydro_hyper3")
+    fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 20, dt=pcfg.fixed_dt(cfg))
+    assert pu.rel_linf(fg, fc).max() <= TOL_100
+
+
+def test_config1_helical_mhd_128_three_steps(oracle_mod):
+    """BASELINE config[1] at full size (128^3 isothermal MHD): 3 full steps against the oracle."""
+    cfg = pcfg.config_helical_mhd_128()
+    fg, fc, sg, sc, _ = pu.run_both(cfg, oracle_mod, 3, dt=pcfg.fixed_dt(cfg), diag_every=1)
+    assert pu.rel_linf(fg, fc).max() <= 1e-11
+    for a, b in zip(sg, sc):
+        for k in ("urms", "brms", "jrms"):
+            assert abs(a[k] - b[k]) <= 1e-11 * abs(b[k])
+
+
+def test_device_synthetic_ic_matches_numpy(oracle_mod):
+    """pcb200_init_synthetic (bench workload generator) == pencil_code_b200.synthetic up to libm ulps"""
+    from pencil_code_b200.gpu import GPU
+    cfg = _cfg("mhd_entropy")
+    f = np.zeros(synthetic.farray_shape(cfg))
+    g = GPU(cfg)
+    g.initialize_GPU(f, nt=0)
+    g.init_synthetic(12345)
+    g.copy_farray_from_GPU(f)
+    g.finalize_GPU()
+    ref = synthetic.initial_condition(cfg, seed=12345)
+    assert np.abs(pu.interior(f) - pu.interior(ref)).max() < 1e-15
+
+
+def test_zero_velocity_uniform_state_is_steady(oracle_mod):
+    """edge case: uniform state has zero RHS; f must stay bit-identical through a step"""
+    from pencil_code_b200.gpu import GPU
+    cfg = _cfg("mhd_entropy")
+    f = np.zeros(synthetic.farray_shape(cfg))
+    f[3] = 0.5
+    f0 = f.copy()
+    g = GPU(cfg)
+    g.initialize_GPU(f)
+    g.time_step(f, 0.01, False, 0.0)
+    g.copy_farray_from_GPU(f)
+    g.finalize_GPU()
+    assert np.array_equal(f, f0)
