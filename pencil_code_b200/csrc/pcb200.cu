@@ -4,6 +4,8 @@
 // (/root/reference/src/gpu_astaroth.f90:21-53, gpu_astaroth_ansi.c, astaroth/gpu_astaroth.cc).
 // See include/pcb200.h for the contract and DESIGN.md for the data layout.
 #include "pcb200_device.cuh"
+#include "pcb200_fast.cuh"
+#include <cudaTypedefs.h>
 #include "../../include/pcb200.h"
 
 #include <cmath>
@@ -13,6 +15,7 @@
 #include <cstring>
 #include <dlfcn.h>
 #include <vector>
+#include <algorithm>
 
 namespace pcb200 {
 
@@ -319,6 +322,9 @@ struct State {
   double *df = nullptr;
   int cur = 0;
   double *host_f = nullptr; // retained Fortran f (gpu_astaroth.cc:2040-2059)
+  CUtensorMap tmap[2];      // TMA descriptors of f[0], f[1] (kernel variant 2)
+  int variant = 1;          // kernel actually used (1 = global-load, 2 = smem ring + TMA)
+  int nsm = 148;
   cudaStream_t stream = nullptr, comm_stream = nullptr;
   bool own_stream = false;
   cudaEvent_t ev_ready = nullptr, ev_halo = nullptr;
@@ -413,6 +419,26 @@ static void check_supported() {
   if (S.nranks != c.nprocy * c.nprocz) die("nprocy*nprocz=%d but %d NCCL ranks", c.nprocy * c.nprocz, S.nranks);
 }
 
+// TMA descriptor of one f buffer: 4-D tensor (x,y,z,var), box = one halo'd (38 x 14) plane tile
+static void make_tensor_map(CUtensorMap *tm, double *base) {
+  static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
+  if (!encode) {
+    cudaDriverEntryPointQueryResult qres;
+    void *fn = nullptr;
+    CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (!fn || qres != cudaDriverEntryPointSuccess) die("cuTensorMapEncodeTiled not available from the driver");
+    encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
+  }
+  const Pars &P = S.P;
+  cuuint64_t dims[4] = {(cuuint64_t)P.mx, (cuuint64_t)P.my, (cuuint64_t)P.mz, (cuuint64_t)P.nvar};
+  cuuint64_t strides[3] = {(cuuint64_t)P.sy * 8, (cuuint64_t)P.sz * 8, (cuuint64_t)P.sv * 8};
+  cuuint32_t box[4] = {(cuuint32_t)V2_HX, (cuuint32_t)V2_HY, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                      CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) die("cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+}
+
 // ---------------------------------------------------------------------------
 // launch helpers
 // ---------------------------------------------------------------------------
@@ -420,6 +446,28 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v1(c
   dim3 b(64, 4, 1);
   dim3 g((S.P.nx + b.x - 1) / b.x, (S.P.ny + b.y - 1) / b.y, (a.z_hi - a.z_lo + b.z - 1) / b.z);
   rhs_update_v1<ENT, MAG, HYP, UPW><<<g, b, 0, st>>>(a);
+}
+
+template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v2(const UpdateArgs &a, cudaStream_t st) {
+  typedef V2Layout<ENT, MAG> L;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(rhs_update_v2<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    attr_set = true;
+  }
+  V2Args v;
+  v.fin = a.fin; v.fout = a.fout; v.df = a.df; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
+  v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
+  const int gx = (S.P.nx + V2_TX - 1) / V2_TX, gy = (S.P.ny + V2_TY - 1) / V2_TY;
+  const int nzr = a.z_hi - a.z_lo;
+  // enough blocks for ~4 waves of one CTA per SM, but chunks of at least 16 planes (6-plane preamble each)
+  int nch = (4 * S.nsm + gx * gy - 1) / (gx * gy);
+  nch = std::max(1, std::min(nch, std::max(1, nzr / 16)));
+  v.lz = (nzr + nch - 1) / nch;
+  nch = (nzr + v.lz - 1) / v.lz;
+  dim3 g(gx, gy, nch), b(V2_TX, V2_TY, 1);
+  const CUtensorMap &tm = (a.fin == S.f[0]) ? S.tmap[0] : S.tmap[1];
+  rhs_update_v2<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(tm, v);
 }
 
 static void launch_update(const UpdateArgs &a, cudaStream_t st) {
@@ -438,7 +486,11 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
     e0 = get(); e1 = get();
     CK(cudaEventRecord(e0, st));
   }
-#define DISPATCH(E, M, H, U) launch_update_v1<E, M, H, U>(a, st)
+#define DISPATCH(E, M, H, U)                                   \
+  do {                                                         \
+    if (S.variant == 2) launch_update_v2<E, M, H, U>(a, st);   \
+    else launch_update_v1<E, M, H, U>(a, st);                  \
+  } while (0)
   const int key = (ent ? 8 : 0) | (mag ? 4 : 0) | (hyp ? 2 : 0) | (upw ? 1 : 0);
   switch (key) {
   case 0: DISPATCH(false, false, false, false); break;
@@ -759,9 +811,19 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   CK(cudaMalloc(&S.dt_dev, sizeof(double)));
   CK(cudaMalloc(&S.dt1_dev, sizeof(double)));
   CK(cudaMallocHost(&S.pinned, 64 * sizeof(double)));
-  int nsm = 148;
-  CK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, 0));
+  int nsm = 148, curdev = 0;
+  CK(cudaGetDevice(&curdev));
+  CK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, curdev));
+  S.nsm = nsm;
   S.red_blocks = nsm * 8;
+  // kernel variant: TMA needs 16-byte global strides -> mx even
+  const bool tma_ok = (P.mx % 2 == 0);
+  if (S.cfg.kernel_variant == 2 && !tma_ok) die("kernel_variant=2 needs an even mx=nx+6 (TMA stride alignment)");
+  S.variant = (S.cfg.kernel_variant == 1) ? 1 : (tma_ok ? 2 : 1);
+  if (S.variant == 2) {
+    make_tensor_map(&S.tmap[0], S.f[0]);
+    make_tensor_map(&S.tmap[1], S.f[1]);
+  }
   CK(cudaMalloc(&S.partial, sizeof(double) * S.red_blocks * (DS_NSUM + DM_NMAX)));
   CK(cudaMalloc(&S.diag_dev, sizeof(double) * (DS_NSUM + DM_NMAX)));
   CK(cudaMalloc(&S.fx_dev, sizeof(double2) * (P.mx + P.my + P.mz)));

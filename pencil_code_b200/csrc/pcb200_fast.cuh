@@ -1,0 +1,513 @@
+// pcb200_fast.cuh -- kernel variant 2: (32x8)-cell tiles marched along z, the 7 z-planes of the
+// vector fields staged in a shared-memory ring by TMA (cp.async.bulk.tensor), scalar fields' z taps
+// in a per-thread register pipeline, one fused RHS + 2N-RK3 update per cell.
+//
+// Same arithmetic as rhs_cell (pcb200_device.cuh; reference citations there) but organised around
+// "lines": the 6 taps of one variable along one axis are loaded once and feed der, der2 (and
+// der5/der6/upwind when enabled), deriv.f90:89-171,472-561,855-935,936-1072.
+#pragma once
+#include "pcb200_device.cuh"
+#include <cuda.h>
+
+namespace pcb200 {
+
+// ---- derivatives from a loaded line (c = centre, m[i]/p[i] = taps at -(i+1)/+(i+1)) ------------
+__device__ __forceinline__ double d1_line(const double m[3], const double p[3], int dir) {
+  return cP.d1fac[dir] * (45.0 * (p[0] - m[0]) - 9.0 * (p[1] - m[1]) + (p[2] - m[2]));
+}
+__device__ __forceinline__ double d2_line(double c, const double m[3], const double p[3], int dir) {
+  return cP.d2fac[dir] *
+         ((-490. / 180.) * c + (270. / 180.) * (p[0] + m[0]) + (-27. / 180.) * (p[1] + m[1]) + (2. / 180.) * (p[2] + m[2]));
+}
+__device__ __forceinline__ double d6raw_line(double c, const double m[3], const double p[3]) {
+  return -20.0 * c + 15.0 * (p[0] + m[0]) - 6.0 * (p[1] + m[1]) + (p[2] + m[2]);
+}
+__device__ __forceinline__ double d5_line(const double m[3], const double p[3], int dir) {
+  return cP.d5fac[dir] * (5.0 * (p[0] - m[0]) - 4.0 * (p[1] - m[1]) + (p[2] - m[2]));
+}
+
+// Policy adapter: global memory lines (lets variant-2 physics run on the variant-1 access path)
+struct GlobalLines {
+  const double *__restrict__ c0;
+  __device__ __forceinline__ double c(int k) const { return __ldg(c0 + k * cP.sv); }
+  __device__ __forceinline__ void line(int k, int dir, double m[3], double p[3]) const {
+    const double *q = c0 + k * cP.sv;
+    const long long s = dir == 0 ? 1LL : (dir == 1 ? cP.sy : cP.sz);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      m[i] = __ldg(q - (i + 1) * s);
+      p[i] = __ldg(q + (i + 1) * s);
+    }
+  }
+  __device__ __forceinline__ double dij(int k, int pair) const {
+    GlobalTaps t{c0};
+    return t.dij(k, pair);
+  }
+};
+
+// ---------------------------------------------------------------------------
+// physics on lines.  rhs[] as in rhs_cell.
+// ---------------------------------------------------------------------------
+template <bool ENT, bool MAG, bool HYP, bool UPW, class T>
+__device__ __forceinline__ void rhs_cell_lines(const T &tp, double *__restrict__ rhs, double *__restrict__ fc) {
+  typedef Slots<ENT> S;
+  const Pars &P = cP;
+  const bool hyp_visc = HYP && (P.lvisc_hyper3_simplified || P.lvisc_hyper3_nu_const);
+
+  double u[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { u[i] = tp.c(S::IUX + i); fc[S::IUX + i] = u[i]; }
+  const double au[3] = {fabs(u[0]), fabs(u[1]), fabs(u[2])};
+
+  // ---- lnrho first (its gradient enters sglnrho, hyper3 viscosity and the pressure force)
+  const double lnrho = tp.c(S::ILN);
+  fc[S::ILN] = lnrho;
+  double gl[3], del2lnrho = 0.0, del6lnrho = 0.0, upw_l = 0.0;
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    double m[3], p[3];
+    tp.line(S::ILN, j, m, p);
+    gl[j] = d1_line(m, p, j);
+    if (ENT) del2lnrho += d2_line(lnrho, m, p, j);
+    if (HYP || UPW) {
+      const double r6 = d6raw_line(lnrho, m, p);
+      if (HYP) del6lnrho += P.d6fac[j] * r6;
+      if (UPW) upw_l += au[j] * (P.d6upfac[j] * r6);
+    }
+  }
+
+  // ---- velocity: gradient tensor, laplacian, diagonal second derivatives
+  double uij[3][3], del2u[3], graddivu[3], hyp[3] = {0., 0., 0.}, upw_u[3] = {0., 0., 0.};
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    double d2s = 0.0;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      double m[3], p[3];
+      tp.line(S::IUX + i, j, m, p);
+      uij[i][j] = d1_line(m, p, j);
+      const double d2 = d2_line(u[i], m, p, j);
+      d2s += d2;
+      if (j == i) graddivu[i] = d2; // fjji(i,i)=der2 (sub.f90:2651-2653)
+      if (HYP || UPW) {
+        const double r6 = d6raw_line(u[i], m, p);
+        if (HYP) {
+          hyp[i] += P.d6fac[j] * r6;                                           // del6v
+          if (P.lvisc_hyper3_nu_const) hyp[i] += d5_line(m, p, j) * gl[j];     // uij5glnrho
+        }
+        if (UPW) upw_u[i] += au[j] * (P.d6upfac[j] * r6);
+      }
+    }
+    del2u[i] = d2s;
+  }
+  // mixed derivatives for grad div u: fjji(i,j)=d_i d_j u_j
+  {
+    const double u1_xy = tp.dij(S::IUX + 0, 0), u1_zx = tp.dij(S::IUX + 0, 2);
+    const double u2_xy = tp.dij(S::IUX + 1, 0), u2_yz = tp.dij(S::IUX + 1, 1);
+    const double u3_yz = tp.dij(S::IUX + 2, 1), u3_zx = tp.dij(S::IUX + 2, 2);
+    graddivu[0] += u2_xy + u3_zx;
+    graddivu[1] += u1_xy + u3_yz;
+    graddivu[2] += u1_zx + u2_yz;
+  }
+  const double divu = uij[0][0] + uij[1][1] + uij[2][2];
+  double sij[3][3];
+#pragma unroll
+  for (int j = 0; j < 3; ++j) {
+    sij[j][j] = uij[j][j] - (1. / 3.) * divu;
+#pragma unroll
+    for (int i = j + 1; i < 3; ++i) {
+      sij[i][j] = .5 * (uij[i][j] + uij[j][i]);
+      sij[j][i] = sij[i][j];
+    }
+  }
+  double ru[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    double ugu = u[0] * uij[i][0] + u[1] * uij[i][1] + u[2] * uij[i][2];
+    if (UPW && P.lupw_uu) ugu -= upw_u[i];
+    ru[i] = -ugu;
+  }
+  double uglnrho = u[0] * gl[0] + u[1] * gl[1] + u[2] * gl[2];
+  if (UPW && P.lupw_lnrho) uglnrho -= upw_l;
+
+  // ---- viscosity
+  double sij2 = 0.0;
+  if (P.lvisc_nu_const) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const double sgl = sij[i][0] * gl[0] + sij[i][1] * gl[1] + sij[i][2] * gl[2];
+      ru[i] += P.nu * (del2u[i] + 2. * sgl + (1. / 3.) * graddivu[i]);
+    }
+    if (ENT) {
+      sij2 = sij[0][0] * sij[0][0] + sij[1][1] * sij[1][1] + sij[2][2] * sij[2][2] +
+             2 * (sij[1][0] * sij[1][0] + sij[2][0] * sij[2][0] + sij[2][1] * sij[2][1]);
+    }
+  }
+  if (hyp_visc) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) ru[i] += P.nu_hyper3 * hyp[i];
+  }
+
+  // ---- continuity
+  double rl = (-divu) - uglnrho;
+  if (HYP && P.ldiff_hyper3lnrho) rl += P.diffrho_hyper3 * del6lnrho;
+  rhs[S::ILN] = rl;
+
+  // ---- eos / energy
+  double TT1 = 0.0, rs = 0.0;
+  if (ENT) {
+    const double ss = tp.c(S::ISS);
+    fc[S::ISS] = ss;
+    double gss[3], del2ss = 0.0, upw_s = 0.0;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      double m[3], p[3];
+      tp.line(S::ISS, j, m, p);
+      gss[j] = d1_line(m, p, j);
+      del2ss += d2_line(ss, m, p, j);
+      if (UPW) upw_s += au[j] * (P.d6upfac[j] * d6raw_line(ss, m, p));
+    }
+    const double e = P.cv1 * ss + P.gamma_m1 * (lnrho - P.lnrho0);
+    const double cs2 = P.cs20 * exp(e);
+    TT1 = exp(-(P.lnTT0 + e));
+    double glnTT[3], g2 = 0.0;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      glnTT[j] = P.gamma_m1 * gl[j] + P.cv1 * gss[j];
+      ru[j] += -cs2 * (gl[j] + glnTT[j]) * P.gamma1;
+      g2 += (gl[j] + glnTT[j]) * glnTT[j];
+    }
+    double ugss = u[0] * gss[0] + u[1] * gss[1] + u[2] * gss[2];
+    if (UPW && P.lupw_ss) ugss -= upw_s;
+    rs = -ugss;
+    if (P.lviscosity_heat) rs += TT1 * (2 * P.nu * sij2);
+    if (P.lheatc_chiconst) rs += P.chi * P.cp * ((P.gamma_m1 * del2lnrho + P.cv1 * del2ss) + g2);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) ru[j] += -P.cs20 * gl[j];
+  }
+
+  // ---- magnetic
+  if (MAG) {
+    const bool upa = UPW && P.lupw_aa;
+    double aij[3][3], dd[3][3], upw_a[3] = {0., 0., 0.};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const double a = tp.c(S::IAX + i);
+      fc[S::IAX + i] = a;
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        double m[3], p[3];
+        tp.line(S::IAX + i, j, m, p);
+        aij[i][j] = (i != j || upa) ? d1_line(m, p, j) : 0.0;
+        dd[i][j] = d2_line(a, m, p, j);
+        if (UPW && j != i) upw_a[i] += au[j] * (P.d6upfac[j] * d6raw_line(a, m, p)); // mask=i (magnetic.f90:6301)
+      }
+    }
+    const double bb[3] = {aij[2][1] - aij[1][2], aij[0][2] - aij[2][0], aij[1][0] - aij[0][1]};
+    const double a1_xy = tp.dij(S::IAX + 0, 0), a1_zx = tp.dij(S::IAX + 0, 2);
+    const double a2_xy = tp.dij(S::IAX + 1, 0), a2_yz = tp.dij(S::IAX + 1, 1);
+    const double a3_yz = tp.dij(S::IAX + 2, 1), a3_zx = tp.dij(S::IAX + 2, 2);
+    double jj[3];
+    jj[0] = P.mu01 * ((a2_xy - dd[0][1]) - (dd[0][2] - a3_zx));
+    jj[1] = P.mu01 * ((a3_yz - dd[1][2]) - (dd[1][0] - a1_xy));
+    jj[2] = P.mu01 * ((a1_zx - dd[2][0]) - (dd[2][1] - a2_yz));
+    const double rho1 = exp(-lnrho);
+    if (P.llorentzforce) {
+      ru[0] += rho1 * (jj[1] * bb[2] - jj[2] * bb[1]);
+      ru[1] += rho1 * (jj[2] * bb[0] - jj[0] * bb[2]);
+      ru[2] += rho1 * (jj[0] * bb[1] - jj[1] * bb[0]);
+    }
+    if (ENT && P.lohmic_heat) rs += P.eta * P.mu0 * (jj[0] * jj[0] + jj[1] * jj[1] + jj[2] * jj[2]) * rho1 * TT1;
+    double fres[3] = {0., 0., 0.};
+    if (P.lresi_eta_const) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) fres[i] = P.eta * (dd[i][0] + dd[i][1] + dd[i][2]);
+    }
+    if (!upa) {
+      rhs[S::IAX + 0] = (u[1] * bb[2] - u[2] * bb[1]) + fres[0];
+      rhs[S::IAX + 1] = (u[2] * bb[0] - u[0] * bb[2]) + fres[1];
+      rhs[S::IAX + 2] = (u[0] * bb[1] - u[1] * bb[0]) + fres[2];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        double x = 0.0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+          if (k != j) x += u[k] * (aij[k][j] - aij[j][k]);
+        rhs[S::IAX + j] = (x + upw_a[j]) + fres[j];
+      }
+    }
+  }
+  if (ENT) rhs[S::ISS] = rs;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) rhs[S::IUX + i] = ru[i];
+}
+
+// ---------------------------------------------------------------------------
+// variant 2 tiling constants
+// ---------------------------------------------------------------------------
+constexpr int V2_TX = 32, V2_TY = 8;
+constexpr int V2_HX = V2_TX + 2 * NG, V2_HY = V2_TY + 2 * NG; // 38 x 14 halo'd plane tile
+constexpr int V2_PLANE = V2_HX * V2_HY;                       // 532 doubles (TMA box)
+constexpr int V2_PLANE_PAD = 544;                             // 4352 B = 34 x 128 B (TMA smem alignment)
+constexpr int V2_NSLOT = 8;                                   // planes z-3..z+3 in use + 1 in flight
+constexpr int V2_THREADS = V2_TX * V2_TY;
+constexpr unsigned V2_BOX_BYTES = V2_PLANE * sizeof(double);
+
+template <bool ENT, bool MAG> struct V2Layout {
+  static constexpr int NRING = 3 + (MAG ? 3 : 0); // u (and A): need z-mixed taps -> ring of planes
+  static constexpr int NSCAL = 1 + (ENT ? 1 : 0); // lnrho (and ss): only in-plane taps from smem
+  static constexpr int RING_DOUBLES = V2_NSLOT * NRING * V2_PLANE_PAD;
+  static constexpr int SCAL_DOUBLES = 2 * NSCAL * V2_PLANE_PAD;
+  static constexpr size_t SMEM_BYTES = (size_t)(RING_DOUBLES + SCAL_DOUBLES) * sizeof(double) + (V2_NSLOT + 2) * 8 + 128;
+};
+
+// ---- PTX wrappers (mbarrier + TMA) -----------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *map, uint64_t *bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+          smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+// ---- tap policy on the shared-memory ring ------------------------------------
+template <bool ENT, bool MAG> struct SmemLines {
+  typedef V2Layout<ENT, MAG> L;
+  typedef Slots<ENT> S;
+  const double *ring;   // + thread offset
+  const double *scal;   // current scalar planes + thread offset
+  int so[7];            // element offsets of planes z-3..z+3 inside the ring
+  double lz[7], sz[7];  // register pipelines of lnrho / ss along z
+
+  __device__ __forceinline__ bool is_ring(int k) const { return k < 3 || (MAG && k >= S::IAX); }
+  __device__ __forceinline__ int ridx(int k) const { return k < 3 ? k : 3 + (k - S::IAX); }
+  __device__ __forceinline__ int sidx(int k) const { return k == S::ILN ? 0 : 1; }
+
+  __device__ __forceinline__ double c(int k) const {
+    if (is_ring(k)) return ring[so[3] + ridx(k) * V2_PLANE_PAD];
+    return k == S::ILN ? lz[3] : sz[3];
+  }
+  __device__ __forceinline__ void line(int k, int dir, double m[3], double p[3]) const {
+    if (is_ring(k)) {
+      const int f = ridx(k) * V2_PLANE_PAD;
+      if (dir == 2) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          m[i] = ring[so[2 - i] + f];
+          p[i] = ring[so[4 + i] + f];
+        }
+      } else {
+        const double *q = ring + so[3] + f;
+        const int s = dir == 0 ? 1 : V2_HX;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          m[i] = q[-(i + 1) * s];
+          p[i] = q[(i + 1) * s];
+        }
+      }
+    } else {
+      if (dir == 2) {
+        const double *r = (k == S::ILN) ? lz : sz;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          m[i] = r[2 - i];
+          p[i] = r[4 + i];
+        }
+      } else {
+        const double *q = scal + sidx(k) * V2_PLANE_PAD;
+        const int s = dir == 0 ? 1 : V2_HX;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          m[i] = q[-(i + 1) * s];
+          p[i] = q[(i + 1) * s];
+        }
+      }
+    }
+  }
+  // bidiagonal mixed derivative (ring variables only)
+  __device__ __forceinline__ double dij(int k, int pair) const {
+    const int f = ridx(k) * V2_PLANE_PAD;
+    double g[3];
+    if (pair == 0) {
+      const double *q = ring + so[3] + f;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const int a = (i + 1), b = (i + 1) * V2_HX;
+        g[i] = (q[a + b] - q[-a + b]) + (q[-a - b] - q[a - b]);
+      }
+    } else {
+      const int a1 = pair == 1 ? V2_HX : 1; // in-plane axis: y for yz, x for zx
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const double *qp = ring + so[4 + i] + f, *qm = ring + so[2 - i] + f;
+        const int a = (i + 1) * a1;
+        g[i] = (qp[a] - qp[-a]) + (qm[-a] - qm[a]);
+      }
+    }
+    return cP.dmfac[pair] * (270. * g[0] - 27. * g[1] + 2. * g[2]);
+  }
+};
+
+struct V2Args {
+  const double *fin;
+  double *fout;
+  double *df;
+  const double *dt_dev;
+  double alpha, beta;
+  int read_df, write_df;
+  int z_lo, z_hi, lz; // z range (incl. ghost offset) and chunk length per blockIdx.z
+  Forcing frc;
+};
+
+template <bool ENT, bool MAG, bool HYP, bool UPW>
+__global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_constant__ CUtensorMap tmap, const V2Args a) {
+  typedef V2Layout<ENT, MAG> L;
+  typedef Slots<ENT> S;
+  constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
+  extern __shared__ unsigned char smem_raw[];
+  // 128-byte aligned carve-up (TMA destination alignment)
+  double *ring = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  double *scal = ring + L::RING_DOUBLES;
+  uint64_t *bar_ring = reinterpret_cast<uint64_t *>(scal + L::SCAL_DOUBLES);
+  uint64_t *bar_scal = bar_ring + V2_NSLOT;
+
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * V2_TX + tx;
+  const int bx0 = blockIdx.x * V2_TX, by0 = blockIdx.y * V2_TY; // origin of the halo'd tile (incl. ghosts)
+  const int zc0 = a.z_lo + blockIdx.z * a.lz;
+  const int zc1 = min(zc0 + a.lz, a.z_hi);
+  if (zc0 >= zc1) return;
+  const int ix = bx0 + tx + NG, iy = by0 + ty + NG;
+  const bool active = ix < cP.nx + NG && iy < cP.ny + NG;
+  const int ixc = min(ix, cP.nx + NG - 1), iyc = min(iy, cP.ny + NG - 1); // clamped (register pipelines)
+  const int last_plane = zc1 - 1 + NG;
+
+  if (tid == 0) {
+    for (int s = 0; s < V2_NSLOT; ++s) mbar_init(&bar_ring[s], 1);
+    mbar_init(&bar_scal[0], 1);
+    mbar_init(&bar_scal[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+
+  auto issue_ring = [&](int j) { // ring plane j <-> z = zc0-3+j
+    const int p = zc0 - NG + j;
+    if (p > last_plane) return;
+    const int slot = j % V2_NSLOT;
+    mbar_expect_tx(&bar_ring[slot], L::NRING * V2_BOX_BYTES);
+#pragma unroll
+    for (int f = 0; f < L::NRING; ++f) {
+      const int var = f < 3 ? f : S::IAX + (f - 3);
+      tma_load_4d(ring + (slot * L::NRING + f) * V2_PLANE_PAD, &tmap, &bar_ring[slot], bx0, by0, p, var);
+    }
+  };
+  auto issue_scal = [&](int j) { // scalar plane j <-> z = zc0+j
+    const int p = zc0 + j;
+    if (p >= zc1) return;
+    const int slot = j & 1;
+    mbar_expect_tx(&bar_scal[slot], L::NSCAL * V2_BOX_BYTES);
+    tma_load_4d(scal + (slot * L::NSCAL + 0) * V2_PLANE_PAD, &tmap, &bar_scal[slot], bx0, by0, p, S::ILN);
+    if (ENT) tma_load_4d(scal + (slot * L::NSCAL + 1) * V2_PLANE_PAD, &tmap, &bar_scal[slot], bx0, by0, p, S::ISS);
+  };
+
+  if (tid == 0) {
+    for (int j = 0; j < 7; ++j) issue_ring(j);
+    issue_scal(0);
+  }
+
+  SmemLines<ENT, MAG> tp;
+  const int toff = (ty + NG) * V2_HX + (tx + NG);
+  tp.ring = ring + toff;
+  // register pipelines for the scalars (own column, straight from global; coalesced)
+  const long long col = ixc + cP.sy * iyc;
+  {
+    const double *gl = a.fin + col + S::ILN * cP.sv;
+#pragma unroll
+    for (int d = 0; d < 7; ++d) tp.lz[d] = __ldg(gl + cP.sz * (zc0 - NG + d));
+    if (ENT) {
+      const double *gs = a.fin + col + S::ISS * cP.sv;
+#pragma unroll
+      for (int d = 0; d < 7; ++d) tp.sz[d] = __ldg(gs + cP.sz * (zc0 - NG + d));
+    }
+  }
+  const double dtb = (*a.dt_dev) * a.beta;
+
+  for (int z = zc0; z < zc1; ++z) {
+    const int j0 = z - zc0;
+    if (tid == 0) {
+      issue_ring(j0 + 7);
+      issue_scal(j0 + 1);
+    }
+    // prefetch the scalars' next pipeline entries (plane z+4) early
+    double nl = 0.0, ns = 0.0;
+    if (z + 4 < cP.mz) {
+      nl = __ldg(a.fin + col + S::ILN * cP.sv + cP.sz * (z + 4));
+      if (ENT) ns = __ldg(a.fin + col + S::ISS * cP.sv + cP.sz * (z + 4));
+    }
+    if (j0 == 0) {
+      for (int d = 0; d < 6; ++d) mbar_wait(&bar_ring[d], 0);
+    }
+    mbar_wait(&bar_ring[(j0 + 6) % V2_NSLOT], ((j0 + 6) / V2_NSLOT) & 1);
+    mbar_wait(&bar_scal[j0 & 1], (j0 >> 1) & 1);
+#pragma unroll
+    for (int d = 0; d < 7; ++d) tp.so[d] = ((j0 + d) % V2_NSLOT) * (L::NRING * V2_PLANE_PAD);
+    tp.scal = scal + (j0 & 1) * (L::NSCAL * V2_PLANE_PAD) + toff;
+
+    if (active) {
+      double rhs[NV], fc[NV];
+      rhs_cell_lines<ENT, MAG, HYP, UPW>(tp, rhs, fc);
+      const long long o = ix + cP.sy * iy + cP.sz * z;
+      double force[3] = {0., 0., 0.};
+      if (a.frc.on) {
+        const double2 fx = a.frc.fx[ix], fy = a.frc.fy[iy], fz = a.frc.fz[z];
+        const double xr = fx.x * fy.x - fx.y * fy.y, xi = fx.x * fy.y + fx.y * fy.x;
+        const double re = xr * fz.x - xi * fz.y, im = xr * fz.y + xi * fz.x;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) force[j] = a.frc.fda[j] * (a.frc.coef1[j] * re - a.frc.coef2[j] * im);
+      }
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const long long q = o + k * cP.sv;
+        double d = rhs[k];
+        if (a.read_df) d = a.alpha * a.df[q] + d;
+        if (a.write_df) a.df[q] = d;
+        double fn = fc[k] + dtb * d;
+        if (k < 3) fn += force[k];
+        a.fout[q] = fn;
+      }
+    }
+    // advance the scalar pipelines
+#pragma unroll
+    for (int d = 0; d < 6; ++d) {
+      tp.lz[d] = tp.lz[d + 1];
+      if (ENT) tp.sz[d] = tp.sz[d + 1];
+    }
+    tp.lz[6] = nl;
+    if (ENT) tp.sz[6] = ns;
+    __syncthreads(); // everyone is done with plane z-3's slot and this scalar slot
+  }
+}
+
+} // namespace pcb200
