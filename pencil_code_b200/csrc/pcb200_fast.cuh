@@ -293,20 +293,22 @@ __device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *map, u
 }
 
 // ---- tap policy on the shared-memory ring ------------------------------------
+// All pointers below are derived from the `extern __shared__` array by plain pointer arithmetic, so
+// that the compiler keeps them in the shared address space (LDS with immediate offsets, 32-bit
+// address registers) -- one base pointer per ring plane, every tap a compile-time offset from it.
 template <bool ENT, bool MAG> struct SmemLines {
   typedef V2Layout<ENT, MAG> L;
   typedef Slots<ENT> S;
-  const double *ring;   // + thread offset
-  const double *scal;   // current scalar planes + thread offset
-  int so[7];            // element offsets of planes z-3..z+3 inside the ring
+  const double *pl[7];  // planes z-3..z+3 of ring field 0 at this thread's cell
+  const double *scal;   // current scalar planes (field 0) at this thread's cell
   double lz[7], sz[7];  // register pipelines of lnrho / ss along z
 
-  __device__ __forceinline__ bool is_ring(int k) const { return k < 3 || (MAG && k >= S::IAX); }
-  __device__ __forceinline__ int ridx(int k) const { return k < 3 ? k : 3 + (k - S::IAX); }
-  __device__ __forceinline__ int sidx(int k) const { return k == S::ILN ? 0 : 1; }
+  static __device__ __forceinline__ bool is_ring(int k) { return k < 3 || (MAG && k >= S::IAX); }
+  static __device__ __forceinline__ int ridx(int k) { return k < 3 ? k : 3 + (k - S::IAX); }
+  static __device__ __forceinline__ int sidx(int k) { return k == S::ILN ? 0 : 1; }
 
   __device__ __forceinline__ double c(int k) const {
-    if (is_ring(k)) return ring[so[3] + ridx(k) * V2_PLANE_PAD];
+    if (is_ring(k)) return pl[3][ridx(k) * V2_PLANE_PAD];
     return k == S::ILN ? lz[3] : sz[3];
   }
   __device__ __forceinline__ void line(int k, int dir, double m[3], double p[3]) const {
@@ -315,11 +317,11 @@ template <bool ENT, bool MAG> struct SmemLines {
       if (dir == 2) {
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
-          m[i] = ring[so[2 - i] + f];
-          p[i] = ring[so[4 + i] + f];
+          m[i] = pl[2 - i][f];
+          p[i] = pl[4 + i][f];
         }
       } else {
-        const double *q = ring + so[3] + f;
+        const double *q = pl[3] + f;
         const int s = dir == 0 ? 1 : V2_HX;
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
@@ -351,7 +353,7 @@ template <bool ENT, bool MAG> struct SmemLines {
     const int f = ridx(k) * V2_PLANE_PAD;
     double g[3];
     if (pair == 0) {
-      const double *q = ring + so[3] + f;
+      const double *q = pl[3] + f;
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
         const int a = (i + 1), b = (i + 1) * V2_HX;
@@ -361,7 +363,7 @@ template <bool ENT, bool MAG> struct SmemLines {
       const int a1 = pair == 1 ? V2_HX : 1; // in-plane axis: y for yz, x for zx
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
-        const double *qp = ring + so[4 + i] + f, *qm = ring + so[2 - i] + f;
+        const double *qp = pl[4 + i] + f, *qm = pl[2 - i] + f;
         const int a = (i + 1) * a1;
         g[i] = (qp[a] - qp[-a]) + (qm[-a] - qm[a]);
       }
@@ -381,14 +383,17 @@ struct V2Args {
   Forcing frc;
 };
 
+extern __shared__ __align__(1024) double v2_smem[];
+
 template <bool ENT, bool MAG, bool HYP, bool UPW>
 __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_constant__ CUtensorMap tmap, const V2Args a) {
   typedef V2Layout<ENT, MAG> L;
   typedef Slots<ENT> S;
   constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
-  extern __shared__ unsigned char smem_raw[];
-  // 128-byte aligned carve-up (TMA destination alignment)
-  double *ring = reinterpret_cast<double *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  // carve-up: ring | scalar planes | mbarriers.  The dynamic shared window starts 1024-byte aligned
+  // (no static shared memory in this kernel), which satisfies TMA's 128-byte destination alignment;
+  // checked once below.
+  double *ring = v2_smem;
   double *scal = ring + L::RING_DOUBLES;
   uint64_t *bar_ring = reinterpret_cast<uint64_t *>(scal + L::SCAL_DOUBLES);
   uint64_t *bar_scal = bar_ring + V2_NSLOT;
@@ -404,6 +409,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_cons
   const int last_plane = zc1 - 1 + NG;
 
   if (tid == 0) {
+    if (smem_u32(ring) & 127u) __trap();
     for (int s = 0; s < V2_NSLOT; ++s) mbar_init(&bar_ring[s], 1);
     mbar_init(&bar_scal[0], 1);
     mbar_init(&bar_scal[1], 1);
@@ -433,13 +439,13 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_cons
   };
 
   if (tid == 0) {
+#pragma unroll 1
     for (int j = 0; j < 7; ++j) issue_ring(j);
     issue_scal(0);
   }
 
   SmemLines<ENT, MAG> tp;
   const int toff = (ty + NG) * V2_HX + (tx + NG);
-  tp.ring = ring + toff;
   // register pipelines for the scalars (own column, straight from global; coalesced)
   const long long col = ixc + cP.sy * iyc;
   {
@@ -453,32 +459,39 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_cons
     }
   }
   const double dtb = (*a.dt_dev) * a.beta;
+  const bool rdf = a.read_df != 0 && active;
 
+#pragma unroll 1
   for (int z = zc0; z < zc1; ++z) {
     const int j0 = z - zc0;
     if (tid == 0) {
       issue_ring(j0 + 7);
       issue_scal(j0 + 1);
     }
-    // prefetch the scalars' next pipeline entries (plane z+4) early
+    const long long o = ix + cP.sy * iy + cP.sz * z;
+    // early global loads: this cell's df (consumed at the very end of the iteration) and the
+    // scalars' next pipeline entries (plane z+4)
+    double dfv[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) dfv[k] = rdf ? __ldcs(a.df + o + k * cP.sv) : 0.0;
     double nl = 0.0, ns = 0.0;
     if (z + 4 < cP.mz) {
       nl = __ldg(a.fin + col + S::ILN * cP.sv + cP.sz * (z + 4));
       if (ENT) ns = __ldg(a.fin + col + S::ISS * cP.sv + cP.sz * (z + 4));
     }
     if (j0 == 0) {
+#pragma unroll 1
       for (int d = 0; d < 6; ++d) mbar_wait(&bar_ring[d], 0);
     }
     mbar_wait(&bar_ring[(j0 + 6) % V2_NSLOT], ((j0 + 6) / V2_NSLOT) & 1);
     mbar_wait(&bar_scal[j0 & 1], (j0 >> 1) & 1);
 #pragma unroll
-    for (int d = 0; d < 7; ++d) tp.so[d] = ((j0 + d) % V2_NSLOT) * (L::NRING * V2_PLANE_PAD);
+    for (int d = 0; d < 7; ++d) tp.pl[d] = ring + ((j0 + d) % V2_NSLOT) * (L::NRING * V2_PLANE_PAD) + toff;
     tp.scal = scal + (j0 & 1) * (L::NSCAL * V2_PLANE_PAD) + toff;
 
     if (active) {
       double rhs[NV], fc[NV];
       rhs_cell_lines<ENT, MAG, HYP, UPW>(tp, rhs, fc);
-      const long long o = ix + cP.sy * iy + cP.sz * z;
       double force[3] = {0., 0., 0.};
       if (a.frc.on) {
         const double2 fx = a.frc.fx[ix], fy = a.frc.fy[iy], fz = a.frc.fz[z];
@@ -490,10 +503,9 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_cons
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
         const long long q = o + k * cP.sv;
-        double d = rhs[k];
-        if (a.read_df) d = a.alpha * a.df[q] + d;
-        if (a.write_df) a.df[q] = d;
-        double fn = fc[k] + dtb * d;
+        const double d = a.alpha * dfv[k] + rhs[k]; // timestep.f90:113 (alpha=0 in substep 1)
+        if (a.write_df) __stcs(a.df + q, d);
+        double fn = fc[k] + dtb * d; // timestep.f90:160-161
         if (k < 3) fn += force[k];
         a.fout[q] = fn;
       }
