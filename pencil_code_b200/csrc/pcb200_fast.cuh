@@ -46,22 +46,31 @@ struct GlobalLines {
 };
 
 // ---------------------------------------------------------------------------
-// physics on lines.  rhs[] as in rhs_cell.
+// physics on lines, in two halves so that the magnetic half can run in its own warps (variant 3):
+//   hydro_part : u, lnrho, ss  -> rhs of u (without the Lorentz force), lnrho, ss (without Ohmic heat)
+//   mag_part   : A (+ u centre) -> rhs of A, j x b and j^2
+//   combine    : ru += rho1*(j x b), rs += eta*mu0*j2*rho1*TT1
+// The accumulation order is that of rhs_cell (pcb200_device.cuh).
 // ---------------------------------------------------------------------------
-template <bool ENT, bool MAG, bool HYP, bool UPW, class T>
-__device__ __forceinline__ void rhs_cell_lines(const T &tp, double *__restrict__ rhs, double *__restrict__ fc) {
+struct HydroOut {
+  double u[3], lnrho, TT1;
+};
+
+template <bool ENT, bool HYP, bool UPW, class T>
+__device__ __forceinline__ void hydro_part(const T &tp, double *__restrict__ rhs, double *__restrict__ fc, HydroOut &ho) {
   typedef Slots<ENT> S;
   const Pars &P = cP;
   const bool hyp_visc = HYP && (P.lvisc_hyper3_simplified || P.lvisc_hyper3_nu_const);
 
   double u[3];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { u[i] = tp.c(S::IUX + i); fc[S::IUX + i] = u[i]; }
+  for (int i = 0; i < 3; ++i) { u[i] = tp.c(S::IUX + i); fc[S::IUX + i] = u[i]; ho.u[i] = u[i]; }
   const double au[3] = {fabs(u[0]), fabs(u[1]), fabs(u[2])};
 
   // ---- lnrho first (its gradient enters sglnrho, hyper3 viscosity and the pressure force)
   const double lnrho = tp.c(S::ILN);
   fc[S::ILN] = lnrho;
+  ho.lnrho = lnrho;
   double gl[3], del2lnrho = 0.0, del6lnrho = 0.0, upw_l = 0.0;
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
@@ -154,7 +163,7 @@ __device__ __forceinline__ void rhs_cell_lines(const T &tp, double *__restrict__
   rhs[S::ILN] = rl;
 
   // ---- eos / energy
-  double TT1 = 0.0, rs = 0.0;
+  ho.TT1 = 0.0;
   if (ENT) {
     const double ss = tp.c(S::ISS);
     fc[S::ISS] = ss;
@@ -169,7 +178,8 @@ __device__ __forceinline__ void rhs_cell_lines(const T &tp, double *__restrict__
     }
     const double e = P.cv1 * ss + P.gamma_m1 * (lnrho - P.lnrho0);
     const double cs2 = P.cs20 * exp(e);
-    TT1 = exp(-(P.lnTT0 + e));
+    const double TT1 = exp(-(P.lnTT0 + e));
+    ho.TT1 = TT1;
     double glnTT[3], g2 = 0.0;
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
@@ -179,69 +189,99 @@ __device__ __forceinline__ void rhs_cell_lines(const T &tp, double *__restrict__
     }
     double ugss = u[0] * gss[0] + u[1] * gss[1] + u[2] * gss[2];
     if (UPW && P.lupw_ss) ugss -= upw_s;
-    rs = -ugss;
+    double rs = -ugss;
     if (P.lviscosity_heat) rs += TT1 * (2 * P.nu * sij2);
     if (P.lheatc_chiconst) rs += P.chi * P.cp * ((P.gamma_m1 * del2lnrho + P.cv1 * del2ss) + g2);
+    rhs[S::ISS] = rs;
   } else {
 #pragma unroll
     for (int j = 0; j < 3; ++j) ru[j] += -P.cs20 * gl[j];
   }
-
-  // ---- magnetic
-  if (MAG) {
-    const bool upa = UPW && P.lupw_aa;
-    double aij[3][3], dd[3][3], upw_a[3] = {0., 0., 0.};
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      const double a = tp.c(S::IAX + i);
-      fc[S::IAX + i] = a;
-#pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        double m[3], p[3];
-        tp.line(S::IAX + i, j, m, p);
-        aij[i][j] = (i != j || upa) ? d1_line(m, p, j) : 0.0;
-        dd[i][j] = d2_line(a, m, p, j);
-        if (UPW && j != i) upw_a[i] += au[j] * (P.d6upfac[j] * d6raw_line(a, m, p)); // mask=i (magnetic.f90:6301)
-      }
-    }
-    const double bb[3] = {aij[2][1] - aij[1][2], aij[0][2] - aij[2][0], aij[1][0] - aij[0][1]};
-    const double a1_xy = tp.dij(S::IAX + 0, 0), a1_zx = tp.dij(S::IAX + 0, 2);
-    const double a2_xy = tp.dij(S::IAX + 1, 0), a2_yz = tp.dij(S::IAX + 1, 1);
-    const double a3_yz = tp.dij(S::IAX + 2, 1), a3_zx = tp.dij(S::IAX + 2, 2);
-    double jj[3];
-    jj[0] = P.mu01 * ((a2_xy - dd[0][1]) - (dd[0][2] - a3_zx));
-    jj[1] = P.mu01 * ((a3_yz - dd[1][2]) - (dd[1][0] - a1_xy));
-    jj[2] = P.mu01 * ((a1_zx - dd[2][0]) - (dd[2][1] - a2_yz));
-    const double rho1 = exp(-lnrho);
-    if (P.llorentzforce) {
-      ru[0] += rho1 * (jj[1] * bb[2] - jj[2] * bb[1]);
-      ru[1] += rho1 * (jj[2] * bb[0] - jj[0] * bb[2]);
-      ru[2] += rho1 * (jj[0] * bb[1] - jj[1] * bb[0]);
-    }
-    if (ENT && P.lohmic_heat) rs += P.eta * P.mu0 * (jj[0] * jj[0] + jj[1] * jj[1] + jj[2] * jj[2]) * rho1 * TT1;
-    double fres[3] = {0., 0., 0.};
-    if (P.lresi_eta_const) {
-#pragma unroll
-      for (int i = 0; i < 3; ++i) fres[i] = P.eta * (dd[i][0] + dd[i][1] + dd[i][2]);
-    }
-    if (!upa) {
-      rhs[S::IAX + 0] = (u[1] * bb[2] - u[2] * bb[1]) + fres[0];
-      rhs[S::IAX + 1] = (u[2] * bb[0] - u[0] * bb[2]) + fres[1];
-      rhs[S::IAX + 2] = (u[0] * bb[1] - u[1] * bb[0]) + fres[2];
-    } else {
-#pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        double x = 0.0;
-#pragma unroll
-        for (int k = 0; k < 3; ++k)
-          if (k != j) x += u[k] * (aij[k][j] - aij[j][k]);
-        rhs[S::IAX + j] = (x + upw_a[j]) + fres[j];
-      }
-    }
-  }
-  if (ENT) rhs[S::ISS] = rs;
 #pragma unroll
   for (int i = 0; i < 3; ++i) rhs[S::IUX + i] = ru[i];
+}
+
+struct MagOut {
+  double jxb[3], j2;
+};
+
+// u[] = velocity at the cell centre; writes rhs[IAX..IAX+2], fc[IAX..IAX+2]
+template <bool ENT, bool UPW, class T>
+__device__ __forceinline__ void mag_part(const T &tp, const double u[3], double *__restrict__ rhs, double *__restrict__ fc,
+                                         MagOut &mo) {
+  typedef Slots<ENT> S;
+  const Pars &P = cP;
+  const bool upa = UPW && P.lupw_aa;
+  const double au[3] = {fabs(u[0]), fabs(u[1]), fabs(u[2])};
+  double aij[3][3], dd[3][3], upw_a[3] = {0., 0., 0.};
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const double a = tp.c(S::IAX + i);
+    fc[S::IAX + i] = a;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      double m[3], p[3];
+      tp.line(S::IAX + i, j, m, p);
+      aij[i][j] = (i != j || upa) ? d1_line(m, p, j) : 0.0;
+      dd[i][j] = d2_line(a, m, p, j);
+      if (UPW && j != i) upw_a[i] += au[j] * (P.d6upfac[j] * d6raw_line(a, m, p)); // mask=i (magnetic.f90:6301)
+    }
+  }
+  const double bb[3] = {aij[2][1] - aij[1][2], aij[0][2] - aij[2][0], aij[1][0] - aij[0][1]};
+  const double a1_xy = tp.dij(S::IAX + 0, 0), a1_zx = tp.dij(S::IAX + 0, 2);
+  const double a2_xy = tp.dij(S::IAX + 1, 0), a2_yz = tp.dij(S::IAX + 1, 1);
+  const double a3_yz = tp.dij(S::IAX + 2, 1), a3_zx = tp.dij(S::IAX + 2, 2);
+  double jj[3];
+  jj[0] = P.mu01 * ((a2_xy - dd[0][1]) - (dd[0][2] - a3_zx));
+  jj[1] = P.mu01 * ((a3_yz - dd[1][2]) - (dd[1][0] - a1_xy));
+  jj[2] = P.mu01 * ((a1_zx - dd[2][0]) - (dd[2][1] - a2_yz));
+  mo.jxb[0] = jj[1] * bb[2] - jj[2] * bb[1];
+  mo.jxb[1] = jj[2] * bb[0] - jj[0] * bb[2];
+  mo.jxb[2] = jj[0] * bb[1] - jj[1] * bb[0];
+  mo.j2 = jj[0] * jj[0] + jj[1] * jj[1] + jj[2] * jj[2];
+  double fres[3] = {0., 0., 0.};
+  if (P.lresi_eta_const) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) fres[i] = P.eta * (dd[i][0] + dd[i][1] + dd[i][2]);
+  }
+  if (!upa) {
+    rhs[S::IAX + 0] = (u[1] * bb[2] - u[2] * bb[1]) + fres[0];
+    rhs[S::IAX + 1] = (u[2] * bb[0] - u[0] * bb[2]) + fres[1];
+    rhs[S::IAX + 2] = (u[0] * bb[1] - u[1] * bb[0]) + fres[2];
+  } else {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      double x = 0.0;
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+        if (k != j) x += u[k] * (aij[k][j] - aij[j][k]);
+      rhs[S::IAX + j] = (x + upw_a[j]) + fres[j];
+    }
+  }
+}
+
+// Lorentz force and Ohmic heating (magnetic.f90:4870-4888,5531,6138-6144)
+template <bool ENT>
+__device__ __forceinline__ void combine_mag(const HydroOut &ho, const double jxb[3], double j2, double *__restrict__ rhs) {
+  typedef Slots<ENT> S;
+  const Pars &P = cP;
+  const double rho1 = exp(-ho.lnrho);
+  if (P.llorentzforce) {
+#pragma unroll
+    for (int i = 0; i < 3; ++i) rhs[S::IUX + i] += rho1 * jxb[i];
+  }
+  if (ENT && P.lohmic_heat) rhs[S::ISS] += P.eta * P.mu0 * j2 * rho1 * ho.TT1;
+}
+
+template <bool ENT, bool MAG, bool HYP, bool UPW, class T>
+__device__ __forceinline__ void rhs_cell_lines(const T &tp, double *__restrict__ rhs, double *__restrict__ fc) {
+  HydroOut ho;
+  hydro_part<ENT, HYP, UPW>(tp, rhs, fc, ho);
+  if (MAG) {
+    MagOut mo;
+    mag_part<ENT, UPW>(tp, ho.u, rhs, fc, mo);
+    combine_mag<ENT>(ho, mo.jxb, mo.j2, rhs);
+  }
 }
 
 // ---------------------------------------------------------------------------
