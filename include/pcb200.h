@@ -63,7 +63,7 @@ typedef struct pcb200_config {
   /* device selection: -1 = local rank modulo device count */
   int device;
   /* kernel selection: 0 = auto (fastest validated), 1 = reference-order global-load kernel,
-     2 = shared-memory z-marching kernel */
+     2 = shared-memory z-marching kernel, 3 = 2 with the physics split over two warp roles */
   int kernel_variant;
 } pcb200_config;
 

@@ -5,6 +5,7 @@
 // See include/pcb200.h for the contract and DESIGN.md for the data layout.
 #include "pcb200_device.cuh"
 #include "pcb200_fast.cuh"
+#include "pcb200_v3.cuh"
 #include <cudaTypedefs.h>
 #include "../../include/pcb200.h"
 
@@ -323,7 +324,8 @@ struct State {
   int cur = 0;
   double *host_f = nullptr; // retained Fortran f (gpu_astaroth.cc:2040-2059)
   CUtensorMap tmap[2];      // TMA descriptors of f[0], f[1] (kernel variant 2)
-  int variant = 1;          // kernel actually used (1 = global-load, 2 = smem ring + TMA)
+  CUtensorMap tmap3_ring[2], tmap3_scal[2]; // variant 3: 3-variable and {lnrho,ss} boxes
+  int variant = 1;          // kernel actually used (1 = global-load, 2 = smem ring + TMA, 3 = 2 + role split)
   int nsm = 148;
   cudaStream_t stream = nullptr, comm_stream = nullptr;
   bool own_stream = false;
@@ -420,7 +422,7 @@ static void check_supported() {
 }
 
 // TMA descriptor of one f buffer: 4-D tensor (x,y,z,var), box = one halo'd (38 x 14) plane tile
-static void make_tensor_map(CUtensorMap *tm, double *base) {
+static void make_tensor_map(CUtensorMap *tm, double *base, int box_x = V2_HX, int box_y = V2_HY, int box_v = 1) {
   static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
   if (!encode) {
     cudaDriverEntryPointQueryResult qres;
@@ -432,7 +434,7 @@ static void make_tensor_map(CUtensorMap *tm, double *base) {
   const Pars &P = S.P;
   cuuint64_t dims[4] = {(cuuint64_t)P.mx, (cuuint64_t)P.my, (cuuint64_t)P.mz, (cuuint64_t)P.nvar};
   cuuint64_t strides[3] = {(cuuint64_t)P.sy * 8, (cuuint64_t)P.sz * 8, (cuuint64_t)P.sv * 8};
-  cuuint32_t box[4] = {(cuuint32_t)V2_HX, (cuuint32_t)V2_HY, 1, 1};
+  cuuint32_t box[4] = {(cuuint32_t)box_x, (cuuint32_t)box_y, 1, (cuuint32_t)box_v};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 4, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                       CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -470,6 +472,27 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v2(c
   rhs_update_v2<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(tm, v);
 }
 
+template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v3(const UpdateArgs &a, cudaStream_t st) {
+  typedef V3Layout<ENT, MAG> L;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(rhs_update_v3<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    attr_set = true;
+  }
+  V2Args v;
+  v.fin = a.fin; v.fout = a.fout; v.df = a.df; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
+  v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
+  const int gx = (S.P.nx + V3_TX - 1) / V3_TX, gy = (S.P.ny + V3_TY - 1) / V3_TY;
+  const int nzr = a.z_hi - a.z_lo;
+  int nch = (4 * S.nsm + gx * gy - 1) / (gx * gy);
+  nch = std::max(1, std::min(nch, std::max(1, nzr / 16)));
+  v.lz = (nzr + nch - 1) / nch;
+  nch = (nzr + v.lz - 1) / v.lz;
+  dim3 g(gx, gy, nch), b(V3_TX, V3_TY, MAG ? 2 : 1);
+  const int w = (a.fin == S.f[0]) ? 0 : 1;
+  rhs_update_v3<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(S.tmap3_ring[w], S.tmap3_scal[w], v);
+}
+
 static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   if (a.z_hi <= a.z_lo) return;
   const bool ent = S.cfg.iss >= 0, mag = S.cfg.iax >= 0;
@@ -488,7 +511,8 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   }
 #define DISPATCH(E, M, H, U)                                   \
   do {                                                         \
-    if (S.variant == 2) launch_update_v2<E, M, H, U>(a, st);   \
+    if (S.variant == 3) launch_update_v3<E, M, H, U>(a, st);   \
+    else if (S.variant == 2) launch_update_v2<E, M, H, U>(a, st); \
     else launch_update_v1<E, M, H, U>(a, st);                  \
   } while (0)
   const int key = (ent ? 8 : 0) | (mag ? 4 : 0) | (hyp ? 2 : 0) | (upw ? 1 : 0);
@@ -818,11 +842,19 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   S.red_blocks = nsm * 8;
   // kernel variant: TMA needs 16-byte global strides -> mx even
   const bool tma_ok = (P.mx % 2 == 0);
-  if (S.cfg.kernel_variant == 2 && !tma_ok) die("kernel_variant=2 needs an even mx=nx+6 (TMA stride alignment)");
-  S.variant = (S.cfg.kernel_variant == 1) ? 1 : (tma_ok ? 2 : 1);
+  const int kv = S.cfg.kernel_variant;
+  if (kv < 0 || kv > 3) die("kernel_variant=%d unknown (0 = auto, 1, 2, 3)", kv);
+  if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
+  S.variant = kv ? kv : (tma_ok ? 2 : 1); // auto: variant 2 (measured fastest on 512^3: 9.7 vs 9.5 G cell-substeps/s for 3)
   if (S.variant == 2) {
     make_tensor_map(&S.tmap[0], S.f[0]);
     make_tensor_map(&S.tmap[1], S.f[1]);
+  }
+  if (S.variant == 3) {
+    for (int w = 0; w < 2; ++w) {
+      make_tensor_map(&S.tmap3_ring[w], S.f[w], V3_HX, V3_HY, 3);
+      make_tensor_map(&S.tmap3_scal[w], S.f[w], V3_HX, V3_HY, S.cfg.iss >= 0 ? 2 : 1);
+    }
   }
   CK(cudaMalloc(&S.partial, sizeof(double) * S.red_blocks * (DS_NSUM + DM_NMAX)));
   CK(cudaMalloc(&S.diag_dev, sizeof(double) * (DS_NSUM + DM_NMAX)));

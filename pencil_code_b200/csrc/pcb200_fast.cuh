@@ -56,7 +56,8 @@ struct HydroOut {
   double u[3], lnrho, TT1;
 };
 
-template <bool ENT, bool HYP, bool UPW, class T>
+// UMIX=false: the mixed derivatives of grad div u are computed elsewhere (variant 3: magnetic role)
+template <bool ENT, bool HYP, bool UPW, class T, bool UMIX = true>
 __device__ __forceinline__ void hydro_part(const T &tp, double *__restrict__ rhs, double *__restrict__ fc, HydroOut &ho) {
   typedef Slots<ENT> S;
   const Pars &P = cP;
@@ -110,7 +111,7 @@ __device__ __forceinline__ void hydro_part(const T &tp, double *__restrict__ rhs
     del2u[i] = d2s;
   }
   // mixed derivatives for grad div u: fjji(i,j)=d_i d_j u_j
-  {
+  if (UMIX) {
     const double u1_xy = tp.dij(S::IUX + 0, 0), u1_zx = tp.dij(S::IUX + 0, 2);
     const double u2_xy = tp.dij(S::IUX + 1, 0), u2_yz = tp.dij(S::IUX + 1, 1);
     const double u3_yz = tp.dij(S::IUX + 2, 1), u3_zx = tp.dij(S::IUX + 2, 2);

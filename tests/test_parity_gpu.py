@@ -33,26 +33,28 @@ def _cfg(name, **over):
     return c
 
 
-@pytest.mark.parametrize("variant", [1, 2])
+@pytest.mark.parametrize("variant", [1, 2, 3])
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_one_substep(oracle_mod, name, variant):
-    """variant 1 = global-load kernel, 2 = TMA/shared-memory z-marching kernel (needs even mx)"""
+    """variant 1 = global-load kernel, 2 = TMA/shared-memory z-marching kernel (needs even mx),
+    3 = variant 2 with the physics split over hydro/magnetic warp roles"""
     cfg = _cfg(name)
-    if variant == 2 and cfg["nx"] % 2:
+    if variant >= 2 and cfg["nx"] % 2:
         pytest.skip("TMA variant needs 16-byte row strides (even mx); odd grids use variant 1")
     fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 0, dt=pcfg.fixed_dt(cfg), substeps_only=1, kernel_variant=variant)
     err = pu.rel_linf(fg, fc)
     assert err.max() <= TOL_SUBSTEP, (name, variant, err)
 
 
+@pytest.mark.parametrize("variant", [2, 3])
 @pytest.mark.parametrize("shape", [(32, 8, 4), (64, 16, 40), (70, 9, 5), (6, 6, 6), (34, 10, 17)])
-def test_variant2_tile_edges(oracle_mod, shape):
+def test_tma_variants_tile_edges(oracle_mod, shape, variant):
     """grids that are not multiples of the 32x8 tile, shorter than one tile, and z-chunk remainders"""
     nx, ny, nz = shape
     cfg = pcfg.make_config(nx, True, True, ny=ny, nz=nz, nu=5e-3, eta=4e-3, chi=3e-3, cdt=0.4, cdtv=0.3)
     cfg.update(dx=0.2, dy=0.21, dz=0.19)
-    fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 0, dt=0.01, substeps_only=3, kernel_variant=2)
-    assert pu.rel_linf(fg, fc).max() <= 5e-12, shape
+    fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 0, dt=0.01, substeps_only=3, kernel_variant=variant)
+    assert pu.rel_linf(fg, fc).max() <= 5e-12, (shape, variant)
 
 
 @pytest.mark.parametrize("name", ["iso_mhd", "mhd_entropy", "ragged"])
