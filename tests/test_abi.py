@@ -61,3 +61,24 @@ def test_fortran_module_lists_gpu_h_names():
                  "tf_infer_gpu", "tf_create_model", "tau_snapshots", "tf_load_model", "tf_load_model_checkpoint",
                  "tf_save_model", "tf_save_checkpoint"):
         assert re.search(r"(subroutine|function)\s+%s\b" % name, src), name
+
+
+def test_start_stub_resolves_every_bound_name(tmp_path):
+    """nogpu_b200_ansi.c (linked into start.x, Makefile.src:3139) compiles against include/pcb200.h and
+    defines every C name gpu_b200.f90 binds; each of those names is also exported by libpcb200.so or by the
+    in-tree shim gpu_b200_ansi.c."""
+    import subprocess
+    fdir = os.path.join(ROOT, "pencil_code_b200", "fortran")
+    obj = str(tmp_path / "stub.o")
+    subprocess.check_call(["gcc", "-c", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(fdir, "nogpu_b200_ansi.c"), "-o", obj])
+    nm = subprocess.run(["nm", obj], capture_output=True, text=True, check=True).stdout
+    stub = {l.split()[2] for l in nm.splitlines() if len(l.split()) == 3 and l.split()[1] == "T"}
+    bound = set(re.findall(r'bind\(c,\s*name="([a-z0-9_]+)"\)', open(os.path.join(fdir, "gpu_b200.f90")).read().lower()))
+    assert bound and bound <= stub, sorted(bound - stub)
+    shim = set(re.findall(r"^void (\w+)\(", open(os.path.join(fdir, "gpu_b200_ansi.c")).read(), re.M))
+    L = gpu.load_library()
+    for name in bound:
+        assert name in shim or hasattr(L, name), name
+    patch = open(os.path.join(fdir, "Makefile.src.patch")).read()
+    assert "gpu_b200_ansi.o" in patch and "nogpu_b200_ansi.o" in patch and "-lpcb200" in patch
