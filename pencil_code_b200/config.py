@@ -21,22 +21,24 @@ DEFAULTS = dict(
 
 
 def make_config(n, entropy, magnetic, nu=0.0, eta=0.0, chi=0.0, hyper3=False, upwind=False,
-                ny=None, nz=None, nprocz=1, ipz=0, Lxyz=2 * math.pi, xyz0=-math.pi, **over):
-    """Periodic cube of n^3 global cells (or n x ny x nz), z-slab decomposed over nprocz ranks.
+                ny=None, nz=None, nprocz=1, ipz=0, nprocy=1, ipy=0, Lxyz=2 * math.pi, xyz0=-math.pi, **over):
+    """Periodic cube of n^3 global cells (or n x ny x nz), decomposed into nprocy x nprocz yz-pencils
+    (nprocy=1: z-slabs); rank = ipy + nprocy*ipz (mpicomm.f90, nprocx=1).
     Grid: dx=L/nxgrid, x_i=x0+(i+1/2)dx (grid.f90:123,149); defaults xyz0=-pi, Lxyz=2pi (cdata.f90:209-211)."""
     nxg = n
     nyg = ny if ny is not None else n
     nzg = nz if nz is not None else n
-    assert nzg % nprocz == 0
+    assert nzg % nprocz == 0 and nyg % nprocy == 0
     c = dict(DEFAULTS)
     dx, dy, dz = Lxyz / nxg, Lxyz / nyg, Lxyz / nzg
     nzl = nzg // nprocz
+    nyl = nyg // nprocy
     nvar = 4 + (1 if entropy else 0) + (3 if magnetic else 0)
     c.update(
-        nx=nxg, ny=nyg, nz=nzl, nprocz=nprocz, ipz=ipz, nvar=nvar,
+        nx=nxg, ny=nyl, nz=nzl, nprocz=nprocz, ipz=ipz, nprocy=nprocy, ipy=ipy, nvar=nvar,
         iux=0, ilnrho=3, iss=4 if entropy else -1, iax=(5 if entropy else 4) if magnetic else -1,
         dx=dx, dy=dy, dz=dz,
-        x0=xyz0 + 0.5 * dx, y0=xyz0 + 0.5 * dy, z0=xyz0 + 0.5 * dz + ipz * nzl * dz,
+        x0=xyz0 + 0.5 * dx, y0=xyz0 + 0.5 * dy + ipy * nyl * dy, z0=xyz0 + 0.5 * dz + ipz * nzl * dz,
         nu=nu, lvisc_nu_const=1 if nu > 0 else 0,
         eta=eta if magnetic else 0.0, lresi_eta_const=1 if (magnetic and eta > 0) else 0,
         chi=chi if entropy else 0.0, lheatc_chiconst=1 if (entropy and chi > 0) else 0,

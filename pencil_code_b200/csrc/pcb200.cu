@@ -129,6 +129,29 @@ __global__ void ghost_fill(double *f, int dir, int nvar) {
   f[dst + k * cP.sv] = f[src + k * cP.sv];
 }
 
+// y-face pack/unpack for yz-pencil decompositions (mpicomm.f90:1604-1731: y-slabs f(:,m1:m1i,n1:n2,:)
+// are mx wide, i.e. carry the x ghosts).  buf[k][izl][r][ix], rows row0..row0+2, interior z only.
+__global__ void pack_y(const double *__restrict__ f, double *__restrict__ buf, int row0, int nvar) {
+  const long long per_var = (long long)NG * cP.mx * cP.nz;
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (tid >= per_var * nvar) return;
+  const int k = (int)(tid / per_var);
+  long long r = tid % per_var;
+  const int ix = (int)(r % cP.mx); r /= cP.mx;
+  const int row = (int)(r % NG), izl = (int)(r / NG);
+  buf[tid] = f[ix + cP.sy * (row0 + row) + cP.sz * (izl + NG) + k * cP.sv];
+}
+__global__ void unpack_y(double *__restrict__ f, const double *__restrict__ buf, int row0, int nvar) {
+  const long long per_var = (long long)NG * cP.mx * cP.nz;
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (tid >= per_var * nvar) return;
+  const int k = (int)(tid / per_var);
+  long long r = tid % per_var;
+  const int ix = (int)(r % cP.mx); r /= cP.mx;
+  const int row = (int)(r % NG), izl = (int)(r / NG);
+  f[ix + cP.sy * (row0 + row) + cP.sz * (izl + NG) + k * cP.sv] = buf[tid];
+}
+
 // ---------------------------------------------------------------------------
 // Courant pre-pass and diagnostics: per-block warp-shuffle reduction, per-block partials,
 // then a single-block fixed-order final reduction (bitwise reproducible).
@@ -330,6 +353,11 @@ struct State {
   cudaStream_t stream = nullptr, comm_stream = nullptr;
   bool own_stream = false;
   cudaEvent_t ev_ready = nullptr, ev_halo = nullptr;
+  bool halo_pending = false; // a z-halo exchange of f[cur] is in flight on comm_stream (ev_halo marks its end)
+  bool split = false;        // interior/boundary split of the fused kernel, z exchange overlapped
+  bool loopback = false;     // test hook PCB200_LOOPBACK=1: exchange code path with self as every neighbour
+  double *ybuf = nullptr;    // 4 staging buffers for y faces (send up/down, recv low/high)
+  size_t ybuf_doubles = 0;
   // dt
   double dt_host = 0.0;
   int ldt = 0;
@@ -409,7 +437,8 @@ static void check_supported() {
   if (c.nx < 1 || c.ny < 1 || c.nz < 1) die("bad grid %d %d %d", c.nx, c.ny, c.nz);
   if (c.nx < NG || c.ny < NG || c.nz < NG) die("local grid smaller than nghost=3 is not supported");
   if (c.nprocx != 1) die("nprocx must be 1 (z-slab / yz-pencil decomposition only)");
-  if (c.nprocy != 1) die("nprocy>1 (yz-pencils) not implemented yet; use z-slabs");
+  if (c.nprocy < 1 || c.nprocz < 1) die("bad decomposition %d x %d", c.nprocy, c.nprocz);
+  if (c.ipy < 0 || c.ipy >= c.nprocy || c.ipz < 0 || c.ipz >= c.nprocz) die("rank position (%d,%d) outside %d x %d", c.ipy, c.ipz, c.nprocy, c.nprocz);
   if (!(c.lperi[0] && c.lperi[1] && c.lperi[2])) die("only periodic boundary conditions ('p') are supported");
   if (c.iux != 0 || c.ilnrho != 3) die("hydro (slots 1-3) and density (slot 4) are required in registration order");
   const bool ent = c.iss >= 0, mag = c.iax >= 0;
@@ -557,32 +586,83 @@ static void launch_ghost(double *f, int dir, cudaStream_t st) {
   S.launches++;
 }
 
-// z-slab halo exchange of 3 xy-planes per variable with the +-z neighbours
-// (replaces initiate/finalize_isendrcv_bdry, mpicomm.f90:1544-2271; z-slabs are contiguous
-// plane ranges of an x-fastest array, so no packing is needed)
-static void exchange_z(double *f, cudaStream_t st) {
-  const Pars &P = S.P;
-  const int up = (S.cfg.ipz + 1) % S.cfg.nprocz, dn = (S.cfg.ipz - 1 + S.cfg.nprocz) % S.cfg.nprocz;
-  const size_t cnt = (size_t)NG * P.sz;
-  NCK(nccl.GroupStart());
-  for (int k = 0; k < P.nvar; ++k) {
-    double *b = f + (size_t)k * P.sv;
-    // send top interior planes up, receive lower ghosts from below
-    NCK(nccl.Send(b + (size_t)P.nz * P.sz, cnt, ncclFloat64, up, S.comm, st));
-    NCK(nccl.Recv(b, cnt, ncclFloat64, dn, S.comm, st));
-    // send bottom interior planes down, receive upper ghosts from above
-    NCK(nccl.Send(b + (size_t)NG * P.sz, cnt, ncclFloat64, dn, S.comm, st));
-    NCK(nccl.Recv(b + (size_t)(NG + P.nz) * P.sz, cnt, ncclFloat64, up, S.comm, st));
+// one neighbour transfer: NCCL send/recv pair, or a device copy in loopback mode (self neighbour)
+static void xfer(const double *sendbuf, double *recvbuf, size_t cnt, int send_to, int recv_from, cudaStream_t st) {
+  if (S.loopback) {
+    CK(cudaMemcpyAsync(recvbuf, sendbuf, cnt * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  } else {
+    NCK(nccl.Send(sendbuf, cnt, ncclFloat64, send_to, S.comm, st));
+    NCK(nccl.Recv(recvbuf, cnt, ncclFloat64, recv_from, S.comm, st));
   }
-  NCK(nccl.GroupEnd());
+}
+static int rank_of(int ipy, int ipz) { // iproc = ipx + nprocx*(ipy + nprocy*ipz), nprocx = 1 (mpicomm.f90)
+  const int ny = S.cfg.nprocy, nz = S.cfg.nprocz;
+  return ((ipy + ny) % ny) + ny * ((ipz + nz) % nz);
 }
 
-// make all ghost zones of buffer f valid (x,y periodic wrap locally; z wrap or exchange)
-static void update_ghosts(double *f, cudaStream_t st) {
+// z-slab halo exchange of 3 xy-planes per variable with the +-z neighbours
+// (replaces initiate/finalize_isendrcv_bdry, mpicomm.f90:1544-2271; z-slabs are contiguous
+// plane ranges of an x-fastest array, so no packing is needed; the planes are mx*my wide and
+// therefore carry the x/y ghosts, i.e. the edges and corners)
+static void exchange_z(double *f, cudaStream_t st) {
+  const Pars &P = S.P;
+  const int up = rank_of(S.cfg.ipy, S.cfg.ipz + 1), dn = rank_of(S.cfg.ipy, S.cfg.ipz - 1);
+  const size_t cnt = (size_t)NG * P.sz;
+  if (!S.loopback) NCK(nccl.GroupStart());
+  for (int k = 0; k < P.nvar; ++k) {
+    double *b = f + (size_t)k * P.sv;
+    xfer(b + (size_t)P.nz * P.sz, b, cnt, up, dn, st);                          // top interior planes -> lower ghosts of "up"
+    xfer(b + (size_t)NG * P.sz, b + (size_t)(NG + P.nz) * P.sz, cnt, dn, up, st); // bottom interior planes -> upper ghosts of "dn"
+  }
+  if (!S.loopback) NCK(nccl.GroupEnd());
+}
+
+// y-face exchange (yz-pencils): pack 3 rows x nz planes x mx, send/recv, unpack
+static void exchange_y(double *f, cudaStream_t st) {
+  const Pars &P = S.P;
+  const int up = rank_of(S.cfg.ipy + 1, S.cfg.ipz), dn = rank_of(S.cfg.ipy - 1, S.cfg.ipz);
+  const size_t cnt = S.ybuf_doubles;
+  double *s_up = S.ybuf, *s_dn = S.ybuf + cnt, *r_lo = S.ybuf + 2 * cnt, *r_hi = S.ybuf + 3 * cnt;
+  const int b = 256;
+  const unsigned g = (unsigned)((cnt + b - 1) / b);
+  pack_y<<<g, b, 0, st>>>(f, s_up, P.ny, P.nvar); // rows m2i..m2 (top interior)
+  pack_y<<<g, b, 0, st>>>(f, s_dn, NG, P.nvar);   // rows m1..m1i (bottom interior)
+  CK(cudaGetLastError());
+  if (!S.loopback) NCK(nccl.GroupStart());
+  xfer(s_up, r_lo, cnt, up, dn, st);
+  xfer(s_dn, r_hi, cnt, dn, up, st);
+  if (!S.loopback) NCK(nccl.GroupEnd());
+  unpack_y<<<g, b, 0, st>>>(f, r_lo, 0, P.nvar);
+  unpack_y<<<g, b, 0, st>>>(f, r_hi, NG + P.ny, P.nvar);
+  CK(cudaGetLastError());
+  S.launches += 4;
+}
+
+// x and y ghosts of buffer f on stream st (x wrap is always local: nprocx = 1)
+static void update_ghosts_xy(double *f, cudaStream_t st) {
   launch_ghost(f, 0, st);
-  launch_ghost(f, 1, st);
-  if (S.cfg.nprocz == 1) launch_ghost(f, 2, st);
-  else exchange_z(f, st);
+  if (S.cfg.nprocy == 1 && !S.loopback) launch_ghost(f, 1, st);
+  else exchange_y(f, st);
+}
+// start the z-halo update of f on the communication stream; ev_halo marks its completion
+static void start_z_halo(double *f, cudaStream_t st) {
+  CK(cudaEventRecord(S.ev_ready, st));
+  CK(cudaStreamWaitEvent(S.comm_stream, S.ev_ready, 0));
+  exchange_z(f, S.comm_stream);
+  CK(cudaEventRecord(S.ev_halo, S.comm_stream));
+  S.halo_pending = true;
+}
+// make stream st see the complete ghost zones of f[cur]
+static void wait_halo(cudaStream_t st) {
+  if (!S.halo_pending) return;
+  CK(cudaStreamWaitEvent(st, S.ev_halo, 0));
+  S.halo_pending = false;
+}
+// make all ghost zones of buffer f valid (x wrap locally; y and z wrap or exchange), in stream order
+static void update_ghosts(double *f, cudaStream_t st) {
+  update_ghosts_xy(f, st);
+  if (S.cfg.nprocz == 1 && !S.loopback) launch_ghost(f, 2, st);
+  else { start_z_halo(f, st); wait_halo(st); }
 }
 
 template <bool ENT, bool MAG> static void launch_cfl_t(const double *f, cudaStream_t st) {
@@ -594,6 +674,7 @@ template <bool ENT, bool MAG> static void launch_diag_t(const double *f, cudaStr
 
 // Courant dt of the step (equ.f90:408 -> sub.f90:4223): dt1 max over all cells and ranks
 static void compute_dt(cudaStream_t st) {
+  wait_halo(st);
   const bool ent = S.cfg.iss >= 0, mag = S.cfg.iax >= 0;
   const double *f = S.f[S.cur];
   if (ent && mag) launch_cfl_t<true, true>(f, st);
@@ -611,6 +692,7 @@ static void compute_dt(cudaStream_t st) {
 }
 
 static void compute_diagnostics(cudaStream_t st) {
+  wait_halo(st);
   const bool ent = S.cfg.iss >= 0, mag = S.cfg.iax >= 0;
   const double *f = S.f[S.cur];
   if (ent && mag) launch_diag_t<true, true>(f, st);
@@ -795,6 +877,7 @@ extern "C" void pcb200_kernel_timing(double *ms, long long *launches, const int 
 
 extern "C" void pcb200_init_synthetic(const int *seed) {
   need_init("pcb200_init_synthetic");
+  wait_halo(S.stream);
   const Pars &P = S.P;
   const long long n = (long long)P.nx * P.ny * P.nz;
   init_synthetic_kernel<<<(unsigned)((n + 255) / 256), 256, 0, S.stream>>>(
@@ -856,6 +939,16 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
       make_tensor_map(&S.tmap3_scal[w], S.f[w], V3_HX, V3_HY, S.cfg.iss >= 0 ? 2 : 1);
     }
   }
+  // halo machinery: yz-pencils need y-face staging; z exchange is overlapped with the interior kernel
+  const char *lb = std::getenv("PCB200_LOOPBACK"); // test hook: run the exchange code path on one GPU (self neighbour)
+  S.loopback = lb && std::atoi(lb) != 0 && S.nranks == 1;
+  if (S.cfg.nprocy > 1 || S.loopback) {
+    S.ybuf_doubles = (size_t)NG * P.mx * P.nz * P.nvar;
+    CK(cudaMalloc(&S.ybuf, 4 * S.ybuf_doubles * sizeof(double)));
+  }
+  const char *ov = std::getenv("PCB200_NO_OVERLAP");
+  S.split = (S.cfg.nprocz > 1 || S.loopback) && P.nz > 2 * NG && !(ov && std::atoi(ov) != 0);
+  S.halo_pending = false;
   CK(cudaMalloc(&S.partial, sizeof(double) * S.red_blocks * (DS_NSUM + DM_NMAX)));
   CK(cudaMalloc(&S.diag_dev, sizeof(double) * (DS_NSUM + DM_NMAX)));
   CK(cudaMalloc(&S.fx_dev, sizeof(double2) * (P.mx + P.my + P.mz)));
@@ -877,6 +970,7 @@ extern "C" void finalize_gpu_c(void) {
   for (cudaEvent_t e : S.ev_pool) cudaEventDestroy(e);
   S.ev_pool.clear();
   cudaFree(S.f[0]); cudaFree(S.f[1]); cudaFree(S.df);
+  if (S.ybuf) cudaFree(S.ybuf);
   cudaFree(S.dt_dev); cudaFree(S.dt1_dev); cudaFree(S.partial); cudaFree(S.diag_dev); cudaFree(S.fx_dev);
   cudaFreeHost(S.pinned); cudaFreeHost(S.ftab_host);
   cudaEventDestroy(S.ev_ready); cudaEventDestroy(S.ev_halo);
@@ -891,6 +985,7 @@ FTN_ALIAS(finalize_gpu_c)
 
 extern "C" void load_farray_c(void) {
   need_init("load_farray_c");
+  wait_halo(S.stream);
   if (!S.host_f) die("load_farray_c: no host f-array was retained by initialize_gpu_c");
   CK(cudaMemcpyAsync(S.f[S.cur], S.host_f, S.nreal * sizeof(double), cudaMemcpyHostToDevice, S.stream));
   update_ghosts(S.f[S.cur], S.stream);
@@ -900,6 +995,7 @@ FTN_ALIAS(load_farray_c)
 
 extern "C" void copy_farray_c(double *f) {
   need_init("copy_farray_c");
+  wait_halo(S.stream);
   CK(cudaMemcpyAsync(f, S.f[S.cur], S.nreal * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
   CK(cudaStreamSynchronize(S.stream));
 }
@@ -963,11 +1059,27 @@ extern "C" void rhs_gpu_c(int *isubstep, double *t) {
     for (int j = 0; j < 3; ++j) { a.frc.coef1[j] = S.coef1[j]; a.frc.coef2[j] = S.coef2[j]; a.frc.fda[j] = S.fda[j]; }
     a.frc.fx = S.fx_dev; a.frc.fy = S.fy_dev; a.frc.fz = S.fz_dev;
   }
-  a.z_lo = NG;
-  a.z_hi = NG + S.P.nz;
-  launch_update(a, st);
-  S.cur ^= 1;
-  update_ghosts(S.f[S.cur], st);
+  if (!S.split) {
+    wait_halo(st);
+    a.z_lo = NG;
+    a.z_hi = NG + S.P.nz;
+    launch_update(a, st);
+    S.cur ^= 1;
+    update_ghosts(S.f[S.cur], st);
+  } else {
+    // interior planes need no z halo: they run while the exchange of f[cur] is still in flight
+    a.z_lo = 2 * NG;
+    a.z_hi = S.P.nz;
+    launch_update(a, st);
+    wait_halo(st);
+    a.z_lo = NG; a.z_hi = 2 * NG;                 // bottom 3 planes
+    launch_update(a, st);
+    a.z_lo = S.P.nz; a.z_hi = NG + S.P.nz;        // top 3 planes
+    launch_update(a, st);
+    S.cur ^= 1;
+    update_ghosts_xy(S.f[S.cur], st);
+    start_z_halo(S.f[S.cur], st);                 // overlaps the next substep's interior kernel
+  }
   if (it == 1 && S.ldt) { // the host driver needs dt for t+=dtsub (timestep.f90:150-152,201)
     double d;
     pcb200_get_dt(&d);
