@@ -138,7 +138,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--n", type=int, default=512)
+    ap.add_argument("--size", "--n", dest="n", type=int, default=512, help="global grid n^3 (use --size under torchrun: --n is ambiguous there)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--kernel-variant", type=int, default=0)
