@@ -412,6 +412,11 @@ static void derive_pars() {
   P.dmfac[0] = (1. / 720.) * d1[0] * d1[1];
   P.dmfac[1] = (1. / 720.) * d1[1] * d1[2];
   P.dmfac[2] = (1. / 720.) * d1[2] * d1[0];
+  for (int j = 0; j < 3; ++j) {
+    const double w1[3] = {45.0, -9.0, 1.0}, w2[4] = {-490. / 180., 270. / 180., -27. / 180., 2. / 180.}, wm[3] = {270., -27., 2.};
+    for (int i = 0; i < 3; ++i) { P.d1c[j][i] = P.d1fac[j] * w1[i]; P.dmc[j][i] = P.dmfac[j] * wm[i]; }
+    for (int i = 0; i < 4; ++i) P.d2c[j][i] = P.d2fac[j] * w2[i];
+  }
   P.dxyz_2 = d1[0] * d1[0] + d1[1] * d1[1] + d1[2] * d1[2];
   P.dxyz_4 = std::pow(d1[0], 4) + std::pow(d1[1], 4) + std::pow(d1[2], 4);
   P.dxyz_6 = std::pow(d1[0], 6) + std::pow(d1[1], 6) + std::pow(d1[2], 6);
@@ -479,11 +484,11 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v1(c
   rhs_update_v1<ENT, MAG, HYP, UPW><<<g, b, 0, st>>>(a);
 }
 
-template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v2(const UpdateArgs &a, cudaStream_t st) {
+template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false> static void launch_update_v2(const UpdateArgs &a, cudaStream_t st) {
   typedef V2Layout<ENT, MAG> L;
   static bool attr_set = false;
   if (!attr_set) {
-    CK(cudaFuncSetAttribute(rhs_update_v2<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    CK(cudaFuncSetAttribute(rhs_update_v2<ENT, MAG, HYP, UPW, TRAIL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
     attr_set = true;
   }
   V2Args v;
@@ -498,7 +503,7 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v2(c
   nch = (nzr + v.lz - 1) / v.lz;
   dim3 g(gx, gy, nch), b(V2_TX, V2_TY, 1);
   const CUtensorMap &tm = (a.fin == S.f[0]) ? S.tmap[0] : S.tmap[1];
-  rhs_update_v2<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(tm, v);
+  rhs_update_v2<ENT, MAG, HYP, UPW, TRAIL><<<g, b, L::SMEM_BYTES, st>>>(tm, v);
 }
 
 template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v3(const UpdateArgs &a, cudaStream_t st) {
@@ -540,7 +545,8 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   }
 #define DISPATCH(E, M, H, U)                                   \
   do {                                                         \
-    if (S.variant == 3) launch_update_v3<E, M, H, U>(a, st);   \
+    if (S.variant == 4) launch_update_v2<E, M, H, U, true>(a, st); \
+    else if (S.variant == 3) launch_update_v3<E, M, H, U>(a, st);   \
     else if (S.variant == 2) launch_update_v2<E, M, H, U>(a, st); \
     else launch_update_v1<E, M, H, U>(a, st);                  \
   } while (0)
@@ -926,10 +932,10 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   // kernel variant: TMA needs 16-byte global strides -> mx even
   const bool tma_ok = (P.mx % 2 == 0);
   const int kv = S.cfg.kernel_variant;
-  if (kv < 0 || kv > 3) die("kernel_variant=%d unknown (0 = auto, 1, 2, 3)", kv);
+  if (kv < 0 || kv > 4) die("kernel_variant=%d unknown (0 = auto, 1, 2, 3, 4)", kv);
   if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
   S.variant = kv ? kv : (tma_ok ? 2 : 1); // auto: variant 2 (measured fastest on 512^3: 9.7 vs 9.5 G cell-substeps/s for 3)
-  if (S.variant == 2) {
+  if (S.variant == 2 || S.variant == 4) {
     make_tensor_map(&S.tmap[0], S.f[0]);
     make_tensor_map(&S.tmap[1], S.f[1]);
   }

@@ -31,6 +31,10 @@ struct Pars {
   double d6fac[3];      // d_j^-6                   der6
   double d6upfac[3];    // (1/60)*d_j^-1            der6 upwind
   double d5fac[3];      // (1/2)/d_j^5              der5
+  // metric factors folded into the stencil weights (variants 2 and 3: one multiply less per derivative)
+  double d1c[3][3];     // d1fac * (45, -9, 1)
+  double d2c[3][4];     // d2fac * (-490, 270, -27, 2)/180
+  double dmc[3][3];     // dmfac * (270, -27, 2)
   double dline_1[3];
   double dxyz_2, dxyz_4, dxyz_6;
   double cs20, gamma, gamma1, gamma_m1, cp, cp1, cv1, lnrho0, lnTT0;

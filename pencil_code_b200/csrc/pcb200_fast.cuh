@@ -13,11 +13,10 @@ namespace pcb200 {
 
 // ---- derivatives from a loaded line (c = centre, m[i]/p[i] = taps at -(i+1)/+(i+1)) ------------
 __device__ __forceinline__ double d1_line(const double m[3], const double p[3], int dir) {
-  return cP.d1fac[dir] * (45.0 * (p[0] - m[0]) - 9.0 * (p[1] - m[1]) + (p[2] - m[2]));
+  return cP.d1c[dir][0] * (p[0] - m[0]) + (cP.d1c[dir][1] * (p[1] - m[1]) + cP.d1c[dir][2] * (p[2] - m[2]));
 }
 __device__ __forceinline__ double d2_line(double c, const double m[3], const double p[3], int dir) {
-  return cP.d2fac[dir] *
-         ((-490. / 180.) * c + (270. / 180.) * (p[0] + m[0]) + (-27. / 180.) * (p[1] + m[1]) + (2. / 180.) * (p[2] + m[2]));
+  return (cP.d2c[dir][0] * c + cP.d2c[dir][1] * (p[0] + m[0])) + (cP.d2c[dir][2] * (p[1] + m[1]) + cP.d2c[dir][3] * (p[2] + m[2]));
 }
 __device__ __forceinline__ double d6raw_line(double c, const double m[3], const double p[3]) {
   return -20.0 * c + 15.0 * (p[0] + m[0]) - 6.0 * (p[1] + m[1]) + (p[2] + m[2]);
@@ -28,6 +27,7 @@ __device__ __forceinline__ double d5_line(const double m[3], const double p[3], 
 
 // Policy adapter: global memory lines (lets variant-2 physics run on the variant-1 access path)
 struct GlobalLines {
+  static constexpr bool TRAIL = false;
   const double *__restrict__ c0;
   __device__ __forceinline__ double c(int k) const { return __ldg(c0 + k * cP.sv); }
   __device__ __forceinline__ void line(int k, int dir, double m[3], double p[3]) const {
@@ -58,9 +58,11 @@ struct HydroOut {
 
 // UMIX=false: the mixed derivatives of grad div u are computed elsewhere (variant 3: magnetic role)
 template <bool ENT, bool HYP, bool UPW, class T, bool UMIX = true>
-__device__ __forceinline__ void hydro_part(const T &tp, double *__restrict__ rhs, double *__restrict__ fc, HydroOut &ho) {
+__device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, double *__restrict__ fc, HydroOut &ho) {
   typedef Slots<ENT> S;
   const Pars &P = cP;
+  double tg[3] = {0., 0., 0.}; // trailing halves of the z-mixed derivatives of grad div u (TRAIL policies)
+  if (T::TRAIL && UMIX) tp.trail_pop(0, tg);
   const bool hyp_visc = HYP && (P.lvisc_hyper3_simplified || P.lvisc_hyper3_nu_const);
 
   double u[3];
@@ -96,6 +98,12 @@ __device__ __forceinline__ void hydro_part(const T &tp, double *__restrict__ rhs
       double m[3], p[3];
       tp.line(S::IUX + i, j, m, p);
       uij[i][j] = d1_line(m, p, j);
+      if (T::TRAIL && UMIX) { // in-plane differences of this plane feed the outputs of planes z+1..z+3
+        if (i == 2 && j == 0) tp.trail_add(0, 0, 2, m, p);
+        if (i == 2 && j == 1) tp.trail_add(0, 1, 1, m, p);
+        if (i == 0 && j == 0) tp.trail_add(0, 2, 2, m, p);
+        if (i == 1 && j == 1) tp.trail_add(0, 2, 1, m, p);
+      }
       const double d2 = d2_line(u[i], m, p, j);
       d2s += d2;
       if (j == i) graddivu[i] = d2; // fjji(i,i)=der2 (sub.f90:2651-2653)
@@ -111,7 +119,12 @@ __device__ __forceinline__ void hydro_part(const T &tp, double *__restrict__ rhs
     del2u[i] = d2s;
   }
   // mixed derivatives for grad div u: fjji(i,j)=d_i d_j u_j
-  if (UMIX) {
+  if (UMIX && T::TRAIL) {
+    tp.lead(0, tg); // + leading halves, read from the planes z+1..z+3 of the ring
+    graddivu[0] += tp.dij(S::IUX + 1, 0) + tg[0];
+    graddivu[1] += tp.dij(S::IUX + 0, 0) + tg[1];
+    graddivu[2] += tg[2];
+  } else if (UMIX) {
     const double u1_xy = tp.dij(S::IUX + 0, 0), u1_zx = tp.dij(S::IUX + 0, 2);
     const double u2_xy = tp.dij(S::IUX + 1, 0), u2_yz = tp.dij(S::IUX + 1, 1);
     const double u3_yz = tp.dij(S::IUX + 2, 1), u3_zx = tp.dij(S::IUX + 2, 2);
@@ -208,10 +221,12 @@ struct MagOut {
 
 // u[] = velocity at the cell centre; writes rhs[IAX..IAX+2], fc[IAX..IAX+2]
 template <bool ENT, bool UPW, class T>
-__device__ __forceinline__ void mag_part(const T &tp, const double u[3], double *__restrict__ rhs, double *__restrict__ fc,
+__device__ __forceinline__ void mag_part(T &tp, const double u[3], double *__restrict__ rhs, double *__restrict__ fc,
                                          MagOut &mo) {
   typedef Slots<ENT> S;
   const Pars &P = cP;
+  double tg[3] = {0., 0., 0.};
+  if (T::TRAIL) tp.trail_pop(1, tg);
   const bool upa = UPW && P.lupw_aa;
   const double au[3] = {fabs(u[0]), fabs(u[1]), fabs(u[2])};
   double aij[3][3], dd[3][3], upw_a[3] = {0., 0., 0.};
@@ -223,19 +238,32 @@ __device__ __forceinline__ void mag_part(const T &tp, const double u[3], double 
     for (int j = 0; j < 3; ++j) {
       double m[3], p[3];
       tp.line(S::IAX + i, j, m, p);
+      if (T::TRAIL) {
+        if (i == 2 && j == 0) tp.trail_add(1, 0, 2, m, p);
+        if (i == 2 && j == 1) tp.trail_add(1, 1, 1, m, p);
+        if (i == 0 && j == 0) tp.trail_add(1, 2, 2, m, p);
+        if (i == 1 && j == 1) tp.trail_add(1, 2, 1, m, p);
+      }
       aij[i][j] = (i != j || upa) ? d1_line(m, p, j) : 0.0;
       dd[i][j] = d2_line(a, m, p, j);
       if (UPW && j != i) upw_a[i] += au[j] * (P.d6upfac[j] * d6raw_line(a, m, p)); // mask=i (magnetic.f90:6301)
     }
   }
   const double bb[3] = {aij[2][1] - aij[1][2], aij[0][2] - aij[2][0], aij[1][0] - aij[0][1]};
-  const double a1_xy = tp.dij(S::IAX + 0, 0), a1_zx = tp.dij(S::IAX + 0, 2);
-  const double a2_xy = tp.dij(S::IAX + 1, 0), a2_yz = tp.dij(S::IAX + 1, 1);
-  const double a3_yz = tp.dij(S::IAX + 2, 1), a3_zx = tp.dij(S::IAX + 2, 2);
   double jj[3];
-  jj[0] = P.mu01 * ((a2_xy - dd[0][1]) - (dd[0][2] - a3_zx));
-  jj[1] = P.mu01 * ((a3_yz - dd[1][2]) - (dd[1][0] - a1_xy));
-  jj[2] = P.mu01 * ((a1_zx - dd[2][0]) - (dd[2][1] - a2_yz));
+  if (T::TRAIL) { // jj = mu01*(grad div A - del2 A); z-mixed parts = leading (ring) + trailing (accumulators) halves
+    tp.lead(1, tg);
+    jj[0] = P.mu01 * ((tp.dij(S::IAX + 1, 0) + tg[0]) - (dd[0][1] + dd[0][2]));
+    jj[1] = P.mu01 * ((tp.dij(S::IAX + 0, 0) + tg[1]) - (dd[1][2] + dd[1][0]));
+    jj[2] = P.mu01 * (tg[2] - (dd[2][0] + dd[2][1]));
+  } else {
+    const double a1_xy = tp.dij(S::IAX + 0, 0), a1_zx = tp.dij(S::IAX + 0, 2);
+    const double a2_xy = tp.dij(S::IAX + 1, 0), a2_yz = tp.dij(S::IAX + 1, 1);
+    const double a3_yz = tp.dij(S::IAX + 2, 1), a3_zx = tp.dij(S::IAX + 2, 2);
+    jj[0] = P.mu01 * ((a2_xy - dd[0][1]) - (dd[0][2] - a3_zx));
+    jj[1] = P.mu01 * ((a3_yz - dd[1][2]) - (dd[1][0] - a1_xy));
+    jj[2] = P.mu01 * ((a1_zx - dd[2][0]) - (dd[2][1] - a2_yz));
+  }
   mo.jxb[0] = jj[1] * bb[2] - jj[2] * bb[1];
   mo.jxb[1] = jj[2] * bb[0] - jj[0] * bb[2];
   mo.jxb[2] = jj[0] * bb[1] - jj[1] * bb[0];
@@ -275,7 +303,7 @@ __device__ __forceinline__ void combine_mag(const HydroOut &ho, const double jxb
 }
 
 template <bool ENT, bool MAG, bool HYP, bool UPW, class T>
-__device__ __forceinline__ void rhs_cell_lines(const T &tp, double *__restrict__ rhs, double *__restrict__ fc) {
+__device__ __forceinline__ void rhs_cell_lines(T &tp, double *__restrict__ rhs, double *__restrict__ fc) {
   HydroOut ho;
   hydro_part<ENT, HYP, UPW>(tp, rhs, fc, ho);
   if (MAG) {
@@ -333,16 +361,79 @@ __device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *map, u
       : "memory");
 }
 
+// named barriers: producers arrive without blocking, only the consumer waits
+__device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void named_bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+
 // ---- tap policy on the shared-memory ring ------------------------------------
 // All pointers below are derived from the `extern __shared__` array by plain pointer arithmetic, so
 // that the compiler keeps them in the shared address space (LDS with immediate offsets, 32-bit
 // address registers) -- one base pointer per ring plane, every tap a compile-time offset from it.
-template <bool ENT, bool MAG> struct SmemLines {
+// TRAIL_ = true (kernel variant 4): "lead/trail" evaluation of the z-mixed bidiagonal derivatives
+//   d_zx f(z) = sum_k w_k [Dx_k f(z+k) - Dx_k f(z-k)],  Dx_k f(z') = f(x+k,y,z') - f(x-k,y,z')   (deriv.f90:1400-1452)
+// The leading half is read from the ring planes z+1..z+3; the trailing half is accumulated, one plane at a
+// time, from the in-plane differences that the first derivatives of the centre plane form anyway
+// (9 accumulators per vector field) -- 48 of 282 LDS.64 per cell less.
+template <bool ENT, bool MAG, bool TRAIL_ = false> struct SmemLines {
   typedef V2Layout<ENT, MAG> L;
   typedef Slots<ENT> S;
+  static constexpr bool TRAIL = TRAIL_;
   const double *pl[7];  // planes z-3..z+3 of ring field 0 at this thread's cell
   const double *scal;   // current scalar planes (field 0) at this thread's cell
   double lz[7], sz[7];  // register pipelines of lnrho / ss along z
+  double T[MAG ? 2 : 1][3][3]; // [u|A][component of grad div][output plane z+j]: trailing halves (TRAIL only)
+
+  static __device__ __forceinline__ int gfield(int g) { return g == 0 ? 0 : 3 * V2_PLANE_PAD; } // ring offset of v_x
+  __device__ __forceinline__ void trail_zero() {
+#pragma unroll
+    for (int g = 0; g < (MAG ? 2 : 1); ++g)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) T[g][c][j] = 0.0;
+  }
+  // accumulators of the output plane -> out[], then shift by one plane
+  __device__ __forceinline__ void trail_pop(int g, double out[3]) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      out[c] = T[g][c][0];
+      T[g][c][0] = T[g][c][1];
+      T[g][c][1] = T[g][c][2];
+      T[g][c][2] = 0.0;
+    }
+  }
+  // differences p[k]-m[k] of the centre plane contribute -w_k D_k to the outputs of planes z+k
+  __device__ __forceinline__ void trail_add(int g, int c, int pair, const double m[3], const double p[3]) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) T[g][c][j] -= cP.dmc[pair][j] * (p[j] - m[j]);
+  }
+  // leading halves: planes z+1..z+3 at in-plane offsets +-k
+  __device__ __forceinline__ void lead(int g, double out[3]) const {
+    const int fx = gfield(g), fy = fx + V2_PLANE_PAD, fz = fy + V2_PLANE_PAD;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const double *q = pl[4 + j];
+      const int a = j + 1, b = (j + 1) * V2_HX;
+      out[0] += cP.dmc[2][j] * (q[fz + a] - q[fz - a]);
+      out[1] += cP.dmc[1][j] * (q[fz + b] - q[fz - b]);
+      out[2] += cP.dmc[2][j] * (q[fx + a] - q[fx - a]) + cP.dmc[1][j] * (q[fy + b] - q[fy - b]);
+    }
+  }
+  // first plane of a z chunk: contributions of the planes z-3..z-1 (ring planes 0..2) to the outputs z..z+2
+  __device__ __forceinline__ void trail_prologue(int g) {
+    const int fx = gfield(g), fy = fx + V2_PLANE_PAD, fz = fy + V2_PLANE_PAD;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const double *q = pl[d];
+#pragma unroll
+      for (int k = 3 - d; k <= 3; ++k) {
+        const int j = d - 3 + k, a = k, b = k * V2_HX;
+        T[g][0][j] -= cP.dmc[2][k - 1] * (q[fz + a] - q[fz - a]);
+        T[g][1][j] -= cP.dmc[1][k - 1] * (q[fz + b] - q[fz - b]);
+        T[g][2][j] -= cP.dmc[2][k - 1] * (q[fx + a] - q[fx - a]) + cP.dmc[1][k - 1] * (q[fy + b] - q[fy - b]);
+      }
+    }
+  }
 
   static __device__ __forceinline__ bool is_ring(int k) { return k < 3 || (MAG && k >= S::IAX); }
   static __device__ __forceinline__ int ridx(int k) { return k < 3 ? k : 3 + (k - S::IAX); }
@@ -409,7 +500,7 @@ template <bool ENT, bool MAG> struct SmemLines {
         g[i] = (qp[a] - qp[-a]) + (qm[-a] - qm[a]);
       }
     }
-    return cP.dmfac[pair] * (270. * g[0] - 27. * g[1] + 2. * g[2]);
+    return cP.dmc[pair][0] * g[0] + (cP.dmc[pair][1] * g[1] + cP.dmc[pair][2] * g[2]);
   }
 };
 
@@ -426,7 +517,7 @@ struct V2Args {
 
 extern __shared__ __align__(1024) double v2_smem[];
 
-template <bool ENT, bool MAG, bool HYP, bool UPW>
+template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false>
 __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_constant__ CUtensorMap tmap, const V2Args a) {
   typedef V2Layout<ENT, MAG> L;
   typedef Slots<ENT> S;
@@ -485,7 +576,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_cons
     issue_scal(0);
   }
 
-  SmemLines<ENT, MAG> tp;
+  SmemLines<ENT, MAG, TRAIL> tp;
+  if (TRAIL) tp.trail_zero();
   const int toff = (ty + NG) * V2_HX + (tx + NG);
   // register pipelines for the scalars (own column, straight from global; coalesced)
   const long long col = ixc + cP.sy * iyc;
@@ -505,9 +597,15 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_cons
 #pragma unroll 1
   for (int z = zc0; z < zc1; ++z) {
     const int j0 = z - zc0;
-    if (tid == 0) {
-      issue_ring(j0 + 7);
-      issue_scal(j0 + 1);
+    // slot release + TMA issue: only the first warp waits until every warp has finished plane z-1
+    // (named barriers 1/2 alternate, because a warp may run one plane ahead of the slowest one)
+    if (tid < 32) {
+      if (j0 > 0) named_bar_sync(1 + ((j0 - 1) & 1), V2_THREADS);
+      if (tid == 0) {
+        issue_ring(j0 + 7);
+        issue_scal(j0 + 1);
+      }
+      __syncwarp();
     }
     const long long o = ix + cP.sy * iy + cP.sz * z;
     // early global loads: this cell's df (consumed at the very end of the iteration) and the
@@ -529,6 +627,10 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_cons
 #pragma unroll
     for (int d = 0; d < 7; ++d) tp.pl[d] = ring + ((j0 + d) % V2_NSLOT) * (L::NRING * V2_PLANE_PAD) + toff;
     tp.scal = scal + (j0 & 1) * (L::NSCAL * V2_PLANE_PAD) + toff;
+    if (TRAIL && j0 == 0) {
+      tp.trail_prologue(0);
+      if (MAG) tp.trail_prologue(1);
+    }
 
     if (active) {
       double rhs[NV], fc[NV];
@@ -559,7 +661,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_cons
     }
     tp.lz[6] = nl;
     if (ENT) tp.sz[6] = ns;
-    __syncthreads(); // everyone is done with plane z-3's slot and this scalar slot
+    // this warp is done with plane z-3's ring slot and with this scalar slot
+    if (z + 1 < zc1 && tid >= 32) named_bar_arrive(1 + (j0 & 1), V2_THREADS);
   }
 }
 

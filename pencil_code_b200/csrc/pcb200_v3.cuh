@@ -40,6 +40,10 @@ template <bool ENT, bool MAG> struct V3Layout {
 // tap policy on the v3 layout (same interface as SmemLines)
 template <bool ENT, bool MAG> struct V3Lines {
   typedef Slots<ENT> S;
+  static constexpr bool TRAIL = false;
+  __device__ __forceinline__ void trail_pop(int, double *) {}
+  __device__ __forceinline__ void trail_add(int, int, int, const double *, const double *) {}
+  __device__ __forceinline__ void lead(int, double *) const {}
   const double *pl[7]; // planes z-3..z+3, field u_x, this thread's cell
   const double *scal;  // current {lnrho, ss} planes, this thread's cell
   double lz[7], sz[7]; // z register pipelines of lnrho / ss (hydro role)
@@ -108,12 +112,10 @@ template <bool ENT, bool MAG> struct V3Lines {
         g[i] = (qp[a] - qp[-a]) + (qm[-a] - qm[a]);
       }
     }
-    return cP.dmfac[pair] * (270. * g[0] - 27. * g[1] + 2. * g[2]);
+    return cP.dmc[pair][0] * g[0] + (cP.dmc[pair][1] * g[1] + cP.dmc[pair][2] * g[2]);
   }
 };
 
-__device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void named_bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 
 extern __shared__ __align__(1024) double v3_smem[];
 
