@@ -347,6 +347,7 @@ struct State {
   int cur = 0;
   double *host_f = nullptr; // retained Fortran f (gpu_astaroth.cc:2040-2059)
   CUtensorMap tmap[2];      // TMA descriptors of f[0], f[1] (kernel variant 2)
+  CUtensorMap tmap_df;      // df tiles (32 x 8 x 1 x nvar) for L2 prefetch
   CUtensorMap tmap3_ring[2], tmap3_scal[2]; // variant 3: 3-variable and {lnrho,ss} boxes
   int variant = 1;          // kernel actually used (1 = global-load, 2 = smem ring + TMA, 3 = 2 + role split)
   int nsm = 148;
@@ -355,6 +356,7 @@ struct State {
   cudaEvent_t ev_ready = nullptr, ev_halo = nullptr;
   bool halo_pending = false; // a z-halo exchange of f[cur] is in flight on comm_stream (ev_halo marks its end)
   bool split = false;        // interior/boundary split of the fused kernel, z exchange overlapped
+  int df_prefetch = 1;       // prefetch.global.L2 of df two planes ahead (+5 %); PCB200_DF_PREFETCH=0 disables
   bool loopback = false;     // test hook PCB200_LOOPBACK=1: exchange code path with self as every neighbour
   double *ybuf = nullptr;    // 4 staging buffers for y faces (send up/down, recv low/high)
   size_t ybuf_doubles = 0;
@@ -494,6 +496,7 @@ template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false> static voi
   V2Args v;
   v.fin = a.fin; v.fout = a.fout; v.df = a.df; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
   v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
+  v.df_prefetch = S.df_prefetch;
   const int gx = (S.P.nx + V2_TX - 1) / V2_TX, gy = (S.P.ny + V2_TY - 1) / V2_TY;
   const int nzr = a.z_hi - a.z_lo;
   // enough blocks for ~4 waves of one CTA per SM, but chunks of at least 16 planes (6-plane preamble each)
@@ -503,7 +506,7 @@ template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false> static voi
   nch = (nzr + v.lz - 1) / v.lz;
   dim3 g(gx, gy, nch), b(V2_TX, V2_TY, 1);
   const CUtensorMap &tm = (a.fin == S.f[0]) ? S.tmap[0] : S.tmap[1];
-  rhs_update_v2<ENT, MAG, HYP, UPW, TRAIL><<<g, b, L::SMEM_BYTES, st>>>(tm, v);
+  rhs_update_v2<ENT, MAG, HYP, UPW, TRAIL><<<g, b, L::SMEM_BYTES, st>>>(tm, S.tmap_df, v);
 }
 
 template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v3(const UpdateArgs &a, cudaStream_t st) {
@@ -516,6 +519,7 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v3(c
   V2Args v;
   v.fin = a.fin; v.fout = a.fout; v.df = a.df; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
   v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
+  v.df_prefetch = S.df_prefetch;
   const int gx = (S.P.nx + V3_TX - 1) / V3_TX, gy = (S.P.ny + V3_TY - 1) / V3_TY;
   const int nzr = a.z_hi - a.z_lo;
   int nch = (4 * S.nsm + gx * gy - 1) / (gx * gy);
@@ -934,7 +938,8 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   const int kv = S.cfg.kernel_variant;
   if (kv < 0 || kv > 4) die("kernel_variant=%d unknown (0 = auto, 1, 2, 3, 4)", kv);
   if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
-  S.variant = kv ? kv : (tma_ok ? 2 : 1); // auto: variant 2 (measured fastest on 512^3: 9.7 vs 9.5 G cell-substeps/s for 3)
+  S.variant = kv ? kv : (tma_ok ? 4 : 1); // auto: variant 4 (measured on 512^3: v4 11.2, v2 10.7, v3 9.5 G cell-substeps/s)
+  if (S.variant >= 2) make_tensor_map(&S.tmap_df, S.df, V2_TX, V2_TY, P.nvar);
   if (S.variant == 2 || S.variant == 4) {
     make_tensor_map(&S.tmap[0], S.f[0]);
     make_tensor_map(&S.tmap[1], S.f[1]);
@@ -952,6 +957,8 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
     S.ybuf_doubles = (size_t)NG * P.mx * P.nz * P.nvar;
     CK(cudaMalloc(&S.ybuf, 4 * S.ybuf_doubles * sizeof(double)));
   }
+  const char *dp = std::getenv("PCB200_DF_PREFETCH");
+  S.df_prefetch = dp ? std::atoi(dp) : 1;
   const char *ov = std::getenv("PCB200_NO_OVERLAP");
   S.split = (S.cfg.nprocz > 1 || S.loopback) && P.nz > 2 * NG && !(ov && std::atoi(ov) != 0);
   S.halo_pending = false;

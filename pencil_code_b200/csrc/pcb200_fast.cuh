@@ -361,6 +361,12 @@ __device__ __forceinline__ void tma_load_4d(void *dst, const CUtensorMap *map, u
       : "memory");
 }
 
+// TMA prefetch of a tile into L2 (no shared-memory destination, no LSU instructions)
+__device__ __forceinline__ void tma_prefetch_4d(const CUtensorMap *map, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];" ::"l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
+
 // named barriers: producers arrive without blocking, only the consumer waits
 __device__ __forceinline__ void named_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void named_bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
@@ -512,13 +518,15 @@ struct V2Args {
   double alpha, beta;
   int read_df, write_df;
   int z_lo, z_hi, lz; // z range (incl. ghost offset) and chunk length per blockIdx.z
+  int df_prefetch;    // 1: TMA-prefetch df tiles into L2 two planes ahead
   Forcing frc;
 };
 
 extern __shared__ __align__(1024) double v2_smem[];
 
 template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false>
-__global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_constant__ CUtensorMap tmap, const V2Args a) {
+__global__ void __launch_bounds__(V2_THREADS, 1)
+    rhs_update_v2(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_df, const V2Args a) {
   typedef V2Layout<ENT, MAG> L;
   typedef Slots<ENT> S;
   constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
@@ -604,15 +612,23 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v2(const __grid_cons
       if (tid == 0) {
         issue_ring(j0 + 7);
         issue_scal(j0 + 1);
+        // (UTMAPF.L2 = cp.async.bulk.prefetch.tensor raised "illegal instruction" on sm_100a/driver 580 with this
+        //  FP64 4-D map; df is prefetched with per-thread prefetch.global.L2 below instead)
+        if (a.read_df && a.df_prefetch == 2 && z + 2 < zc1) tma_prefetch_4d(&tmap_df, bx0 + NG, by0 + NG, z + 2, 0); // debug only
       }
       __syncwarp();
     }
     const long long o = ix + cP.sy * iy + cP.sz * z;
-    // early global loads: this cell's df (consumed at the very end of the iteration) and the
-    // scalars' next pipeline entries (plane z+4)
+    // early global loads: this cell's df (consumed at the very end of the iteration) and the scalars' next
+    // pipeline entries (plane z+4).  Measured: loading df late instead (even after an L2 prefetch two planes
+    // ahead) costs 20-40 %, the 16 registers are well spent.
     double dfv[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) dfv[k] = rdf ? __ldcs(a.df + o + k * cP.sv) : 0.0;
+    if (rdf && a.df_prefetch == 1 && z + 2 < zc1) {
+#pragma unroll
+      for (int k = 0; k < NV; ++k) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.df + o + 2 * cP.sz + k * cP.sv));
+    }
     double nl = 0.0, ns = 0.0;
     if (z + 4 < cP.mz) {
       nl = __ldg(a.fin + col + S::ILN * cP.sv + cP.sz * (z + 4));
