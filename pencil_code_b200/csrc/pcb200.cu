@@ -6,6 +6,7 @@
 #include "pcb200_device.cuh"
 #include "pcb200_fast.cuh"
 #include "pcb200_v3.cuh"
+#include "pcb200_v5.cuh"
 #include <cudaTypedefs.h>
 #include "../../include/pcb200.h"
 
@@ -427,6 +428,7 @@ static void derive_pars() {
   P.cp = c.cp; P.cp1 = 1 / c.cp; P.cv1 = c.gamma * P.cp1; P.lnrho0 = c.lnrho0;
   P.lnTT0 = (P.gamma_m1 != 0.0) ? std::log(c.cs20 / (c.cp * P.gamma_m1)) : std::log(c.cs20 / c.cp);
   P.cp = 1 / P.cp1; // p%cp=1/cp1 (eos_idealgas.f90:811)
+  P.TT0_1 = std::exp(-P.lnTT0);
   P.mu0 = c.mu0; P.mu01 = 1. / c.mu0;
   P.nu = c.nu; P.nu_hyper3 = c.nu_hyper3; P.diffrho_hyper3 = c.diffrho_hyper3; P.chi = c.chi; P.eta = c.eta;
   P.cdt = c.cdt; P.cdtv = c.cdtv; P.cdtv2 = c.cdtv2; P.cdtv3 = c.cdtv3;
@@ -509,6 +511,28 @@ template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false> static voi
   rhs_update_v2<ENT, MAG, HYP, UPW, TRAIL><<<g, b, L::SMEM_BYTES, st>>>(tm, S.tmap_df, v);
 }
 
+template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v5(const UpdateArgs &a, cudaStream_t st) {
+  typedef V2Layout<ENT, MAG> L;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(rhs_update_v5<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    attr_set = true;
+  }
+  V2Args v;
+  v.fin = a.fin; v.fout = a.fout; v.df = a.df; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
+  v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
+  v.df_prefetch = S.df_prefetch;
+  const int gx = (S.P.nx + V2_TX - 1) / V2_TX, gy = (S.P.ny + V2_TY - 1) / V2_TY;
+  const int nzr = a.z_hi - a.z_lo;
+  int nch = (4 * S.nsm + gx * gy - 1) / (gx * gy);
+  nch = std::max(1, std::min(nch, std::max(1, nzr / 16)));
+  v.lz = (nzr + nch - 1) / nch;
+  nch = (nzr + v.lz - 1) / v.lz;
+  dim3 g(gx, gy, nch), b(V2_TX, V2_TY, 1);
+  const CUtensorMap &tm = (a.fin == S.f[0]) ? S.tmap[0] : S.tmap[1];
+  rhs_update_v5<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(tm, v);
+}
+
 template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v3(const UpdateArgs &a, cudaStream_t st) {
   typedef V3Layout<ENT, MAG> L;
   static bool attr_set = false;
@@ -549,7 +573,8 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   }
 #define DISPATCH(E, M, H, U)                                   \
   do {                                                         \
-    if (S.variant == 4) launch_update_v2<E, M, H, U, true>(a, st); \
+    if (S.variant == 5) launch_update_v5<E, M, H, U>(a, st);   \
+    else if (S.variant == 4) launch_update_v2<E, M, H, U, true>(a, st); \
     else if (S.variant == 3) launch_update_v3<E, M, H, U>(a, st);   \
     else if (S.variant == 2) launch_update_v2<E, M, H, U>(a, st); \
     else launch_update_v1<E, M, H, U>(a, st);                  \
@@ -936,11 +961,13 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   // kernel variant: TMA needs 16-byte global strides -> mx even
   const bool tma_ok = (P.mx % 2 == 0);
   const int kv = S.cfg.kernel_variant;
-  if (kv < 0 || kv > 4) die("kernel_variant=%d unknown (0 = auto, 1, 2, 3, 4)", kv);
+  if (kv < 0 || kv > 5) die("kernel_variant=%d unknown (0 = auto, 1 ... 5)", kv);
   if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
-  S.variant = kv ? kv : (tma_ok ? 4 : 1); // auto: variant 4 (measured on 512^3: v4 11.2, v2 10.7, v3 9.5 G cell-substeps/s)
+  const bool iso = S.cfg.dx == S.cfg.dy && S.cfg.dy == S.cfg.dz; // variant 5 shares one set of stencil weights
+  S.variant = kv ? kv : (tma_ok ? (iso ? 5 : 4) : 1);
+  if (S.variant == 5 && !iso) S.variant = 4; // anisotropic spacing: same kernel structure with per-direction weights
   if (S.variant >= 2) make_tensor_map(&S.tmap_df, S.df, V2_TX, V2_TY, P.nvar);
-  if (S.variant == 2 || S.variant == 4) {
+  if (S.variant == 2 || S.variant == 4 || S.variant == 5) {
     make_tensor_map(&S.tmap[0], S.f[0]);
     make_tensor_map(&S.tmap[1], S.f[1]);
   }

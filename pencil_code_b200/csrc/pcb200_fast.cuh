@@ -28,6 +28,8 @@ __device__ __forceinline__ double d5_line(const double m[3], const double p[3], 
 // Policy adapter: global memory lines (lets variant-2 physics run on the variant-1 access path)
 struct GlobalLines {
   static constexpr bool TRAIL = false;
+  static __device__ __forceinline__ int dr(int j) { return j; } // index of the per-direction stencil weights
+  static __device__ __forceinline__ int pr(int p) { return p; } // index of the per-pair mixed-derivative weights
   const double *__restrict__ c0;
   __device__ __forceinline__ double c(int k) const { return __ldg(c0 + k * cP.sv); }
   __device__ __forceinline__ void line(int k, int dir, double m[3], double p[3]) const {
@@ -79,12 +81,12 @@ __device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, doub
   for (int j = 0; j < 3; ++j) {
     double m[3], p[3];
     tp.line(S::ILN, j, m, p);
-    gl[j] = d1_line(m, p, j);
-    if (ENT) del2lnrho += d2_line(lnrho, m, p, j);
+    gl[j] = d1_line(m, p, T::dr(j));
+    if (ENT) del2lnrho += d2_line(lnrho, m, p, T::dr(j));
     if (HYP || UPW) {
       const double r6 = d6raw_line(lnrho, m, p);
-      if (HYP) del6lnrho += P.d6fac[j] * r6;
-      if (UPW) upw_l += au[j] * (P.d6upfac[j] * r6);
+      if (HYP) del6lnrho += P.d6fac[T::dr(j)] * r6;
+      if (UPW) upw_l += au[j] * (P.d6upfac[T::dr(j)] * r6);
     }
   }
 
@@ -97,23 +99,23 @@ __device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, doub
     for (int j = 0; j < 3; ++j) {
       double m[3], p[3];
       tp.line(S::IUX + i, j, m, p);
-      uij[i][j] = d1_line(m, p, j);
+      uij[i][j] = d1_line(m, p, T::dr(j));
       if (T::TRAIL && UMIX) { // in-plane differences of this plane feed the outputs of planes z+1..z+3
         if (i == 2 && j == 0) tp.trail_add(0, 0, 2, m, p);
         if (i == 2 && j == 1) tp.trail_add(0, 1, 1, m, p);
         if (i == 0 && j == 0) tp.trail_add(0, 2, 2, m, p);
         if (i == 1 && j == 1) tp.trail_add(0, 2, 1, m, p);
       }
-      const double d2 = d2_line(u[i], m, p, j);
+      const double d2 = d2_line(u[i], m, p, T::dr(j));
       d2s += d2;
       if (j == i) graddivu[i] = d2; // fjji(i,i)=der2 (sub.f90:2651-2653)
       if (HYP || UPW) {
         const double r6 = d6raw_line(u[i], m, p);
         if (HYP) {
-          hyp[i] += P.d6fac[j] * r6;                                           // del6v
-          if (P.lvisc_hyper3_nu_const) hyp[i] += d5_line(m, p, j) * gl[j];     // uij5glnrho
+          hyp[i] += P.d6fac[T::dr(j)] * r6;                                           // del6v
+          if (P.lvisc_hyper3_nu_const) hyp[i] += d5_line(m, p, T::dr(j)) * gl[j];     // uij5glnrho
         }
-        if (UPW) upw_u[i] += au[j] * (P.d6upfac[j] * r6);
+        if (UPW) upw_u[i] += au[j] * (P.d6upfac[T::dr(j)] * r6);
       }
     }
     del2u[i] = d2s;
@@ -186,13 +188,14 @@ __device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, doub
     for (int j = 0; j < 3; ++j) {
       double m[3], p[3];
       tp.line(S::ISS, j, m, p);
-      gss[j] = d1_line(m, p, j);
-      del2ss += d2_line(ss, m, p, j);
-      if (UPW) upw_s += au[j] * (P.d6upfac[j] * d6raw_line(ss, m, p));
+      gss[j] = d1_line(m, p, T::dr(j));
+      del2ss += d2_line(ss, m, p, T::dr(j));
+      if (UPW) upw_s += au[j] * (P.d6upfac[T::dr(j)] * d6raw_line(ss, m, p));
     }
     const double e = P.cv1 * ss + P.gamma_m1 * (lnrho - P.lnrho0);
-    const double cs2 = P.cs20 * exp(e);
-    const double TT1 = exp(-(P.lnTT0 + e));
+    const double ex = exp(e);
+    const double cs2 = P.cs20 * ex;
+    const double TT1 = P.TT0_1 * __drcp_rn(ex); // = exp(-(lnTT0+e)) to 1 ulp, one exp less (eos_idealgas.f90:851-888)
     ho.TT1 = TT1;
     double glnTT[3], g2 = 0.0;
 #pragma unroll
@@ -244,9 +247,9 @@ __device__ __forceinline__ void mag_part(T &tp, const double u[3], double *__res
         if (i == 0 && j == 0) tp.trail_add(1, 2, 2, m, p);
         if (i == 1 && j == 1) tp.trail_add(1, 2, 1, m, p);
       }
-      aij[i][j] = (i != j || upa) ? d1_line(m, p, j) : 0.0;
-      dd[i][j] = d2_line(a, m, p, j);
-      if (UPW && j != i) upw_a[i] += au[j] * (P.d6upfac[j] * d6raw_line(a, m, p)); // mask=i (magnetic.f90:6301)
+      aij[i][j] = (i != j || upa) ? d1_line(m, p, T::dr(j)) : 0.0;
+      dd[i][j] = d2_line(a, m, p, T::dr(j));
+      if (UPW && j != i) upw_a[i] += au[j] * (P.d6upfac[T::dr(j)] * d6raw_line(a, m, p)); // mask=i (magnetic.f90:6301)
     }
   }
   const double bb[3] = {aij[2][1] - aij[1][2], aij[0][2] - aij[2][0], aij[1][0] - aij[0][1]};
@@ -380,10 +383,14 @@ __device__ __forceinline__ void named_bar_arrive(int id, int n) { asm volatile("
 // The leading half is read from the ring planes z+1..z+3; the trailing half is accumulated, one plane at a
 // time, from the in-plane differences that the first derivatives of the centre plane form anyway
 // (9 accumulators per vector field) -- 48 of 282 LDS.64 per cell less.
-template <bool ENT, bool MAG, bool TRAIL_ = false> struct SmemLines {
+template <bool ENT, bool MAG, bool TRAIL_ = false, bool ISO_ = false> struct SmemLines {
   typedef V2Layout<ENT, MAG> L;
   typedef Slots<ENT> S;
   static constexpr bool TRAIL = TRAIL_;
+  // ISO_: dx == dy == dz bit for bit -> one set of stencil weights serves all directions (30 -> 10 constants)
+  static constexpr bool ISO = ISO_;
+  static __device__ __forceinline__ int dr(int j) { return ISO ? 0 : j; }
+  static __device__ __forceinline__ int pr(int p) { return ISO ? 0 : p; }
   const double *pl[7];  // planes z-3..z+3 of ring field 0 at this thread's cell
   const double *scal;   // current scalar planes (field 0) at this thread's cell
   double lz[7], sz[7];  // register pipelines of lnrho / ss along z
@@ -411,7 +418,7 @@ template <bool ENT, bool MAG, bool TRAIL_ = false> struct SmemLines {
   // differences p[k]-m[k] of the centre plane contribute -w_k D_k to the outputs of planes z+k
   __device__ __forceinline__ void trail_add(int g, int c, int pair, const double m[3], const double p[3]) {
 #pragma unroll
-    for (int j = 0; j < 3; ++j) T[g][c][j] -= cP.dmc[pair][j] * (p[j] - m[j]);
+    for (int j = 0; j < 3; ++j) T[g][c][j] -= cP.dmc[pr(pair)][j] * (p[j] - m[j]);
   }
   // leading halves: planes z+1..z+3 at in-plane offsets +-k
   __device__ __forceinline__ void lead(int g, double out[3]) const {
@@ -420,9 +427,9 @@ template <bool ENT, bool MAG, bool TRAIL_ = false> struct SmemLines {
     for (int j = 0; j < 3; ++j) {
       const double *q = pl[4 + j];
       const int a = j + 1, b = (j + 1) * V2_HX;
-      out[0] += cP.dmc[2][j] * (q[fz + a] - q[fz - a]);
-      out[1] += cP.dmc[1][j] * (q[fz + b] - q[fz - b]);
-      out[2] += cP.dmc[2][j] * (q[fx + a] - q[fx - a]) + cP.dmc[1][j] * (q[fy + b] - q[fy - b]);
+      out[0] += cP.dmc[pr(2)][j] * (q[fz + a] - q[fz - a]);
+      out[1] += cP.dmc[pr(1)][j] * (q[fz + b] - q[fz - b]);
+      out[2] += cP.dmc[pr(2)][j] * (q[fx + a] - q[fx - a]) + cP.dmc[pr(1)][j] * (q[fy + b] - q[fy - b]);
     }
   }
   // first plane of a z chunk: contributions of the planes z-3..z-1 (ring planes 0..2) to the outputs z..z+2
@@ -434,9 +441,9 @@ template <bool ENT, bool MAG, bool TRAIL_ = false> struct SmemLines {
 #pragma unroll
       for (int k = 3 - d; k <= 3; ++k) {
         const int j = d - 3 + k, a = k, b = k * V2_HX;
-        T[g][0][j] -= cP.dmc[2][k - 1] * (q[fz + a] - q[fz - a]);
-        T[g][1][j] -= cP.dmc[1][k - 1] * (q[fz + b] - q[fz - b]);
-        T[g][2][j] -= cP.dmc[2][k - 1] * (q[fx + a] - q[fx - a]) + cP.dmc[1][k - 1] * (q[fy + b] - q[fy - b]);
+        T[g][0][j] -= cP.dmc[pr(2)][k - 1] * (q[fz + a] - q[fz - a]);
+        T[g][1][j] -= cP.dmc[pr(1)][k - 1] * (q[fz + b] - q[fz - b]);
+        T[g][2][j] -= cP.dmc[pr(2)][k - 1] * (q[fx + a] - q[fx - a]) + cP.dmc[pr(1)][k - 1] * (q[fy + b] - q[fy - b]);
       }
     }
   }
@@ -506,7 +513,7 @@ template <bool ENT, bool MAG, bool TRAIL_ = false> struct SmemLines {
         g[i] = (qp[a] - qp[-a]) + (qm[-a] - qm[a]);
       }
     }
-    return cP.dmc[pair][0] * g[0] + (cP.dmc[pair][1] * g[1] + cP.dmc[pair][2] * g[2]);
+    return cP.dmc[pr(pair)][0] * g[0] + (cP.dmc[pr(pair)][1] * g[1] + cP.dmc[pr(pair)][2] * g[2]);
   }
 };
 

@@ -41,6 +41,8 @@ template <bool ENT, bool MAG> struct V3Layout {
 template <bool ENT, bool MAG> struct V3Lines {
   typedef Slots<ENT> S;
   static constexpr bool TRAIL = false;
+  static __device__ __forceinline__ int dr(int j) { return j; }
+  static __device__ __forceinline__ int pr(int p) { return p; }
   __device__ __forceinline__ void trail_pop(int, double *) {}
   __device__ __forceinline__ void trail_add(int, int, int, const double *, const double *) {}
   __device__ __forceinline__ void lead(int, double *) const {}
