@@ -429,6 +429,7 @@ static void derive_pars() {
   P.lnTT0 = (P.gamma_m1 != 0.0) ? std::log(c.cs20 / (c.cp * P.gamma_m1)) : std::log(c.cs20 / c.cp);
   P.cp = 1 / P.cp1; // p%cp=1/cp1 (eos_idealgas.f90:811)
   P.TT0_1 = std::exp(-P.lnTT0);
+  { double fact = 1.0; for (int n = 0; n < 14; ++n) { if (n) fact *= n; P.expc[n] = 1.0 / fact; } }
   P.mu0 = c.mu0; P.mu01 = 1. / c.mu0;
   P.nu = c.nu; P.nu_hyper3 = c.nu_hyper3; P.diffrho_hyper3 = c.diffrho_hyper3; P.chi = c.chi; P.eta = c.eta;
   P.cdt = c.cdt; P.cdtv = c.cdtv; P.cdtv2 = c.cdtv2; P.cdtv3 = c.cdtv3;
@@ -512,7 +513,7 @@ template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false> static voi
 }
 
 template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v5(const UpdateArgs &a, cudaStream_t st) {
-  typedef V2Layout<ENT, MAG> L;
+  typedef V5Layout<ENT, MAG> L;
   static bool attr_set = false;
   if (!attr_set) {
     CK(cudaFuncSetAttribute(rhs_update_v5<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
@@ -529,8 +530,8 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v5(c
   v.lz = (nzr + nch - 1) / nch;
   nch = (nzr + v.lz - 1) / v.lz;
   dim3 g(gx, gy, nch), b(V2_TX, V2_TY, 1);
-  const CUtensorMap &tm = (a.fin == S.f[0]) ? S.tmap[0] : S.tmap[1];
-  rhs_update_v5<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(tm, v);
+  const int w = (a.fin == S.f[0]) ? 0 : 1;
+  rhs_update_v5<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(S.tmap3_ring[w], S.tmap3_scal[w], v);
 }
 
 template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v3(const UpdateArgs &a, cudaStream_t st) {
@@ -967,11 +968,11 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   S.variant = kv ? kv : (tma_ok ? (iso ? 5 : 4) : 1);
   if (S.variant == 5 && !iso) S.variant = 4; // anisotropic spacing: same kernel structure with per-direction weights
   if (S.variant >= 2) make_tensor_map(&S.tmap_df, S.df, V2_TX, V2_TY, P.nvar);
-  if (S.variant == 2 || S.variant == 4 || S.variant == 5) {
+  if (S.variant == 2 || S.variant == 4) {
     make_tensor_map(&S.tmap[0], S.f[0]);
     make_tensor_map(&S.tmap[1], S.f[1]);
   }
-  if (S.variant == 3) {
+  if (S.variant == 3 || S.variant == 5) {
     for (int w = 0; w < 2; ++w) {
       make_tensor_map(&S.tmap3_ring[w], S.f[w], V3_HX, V3_HY, 3);
       make_tensor_map(&S.tmap3_scal[w], S.f[w], V3_HX, V3_HY, S.cfg.iss >= 0 ? 2 : 1);

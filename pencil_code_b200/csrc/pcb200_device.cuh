@@ -38,6 +38,7 @@ struct Pars {
   double dline_1[3];
   double dxyz_2, dxyz_4, dxyz_6;
   double cs20, gamma, gamma1, gamma_m1, cp, cp1, cv1, lnrho0, lnTT0, TT0_1; // TT0_1 = exp(-lnTT0)
+  double expc[14];      // 1/n!, n = 0..13 (exp_fast)
   double mu0, mu01;
   double nu, nu_hyper3, diffrho_hyper3, chi, eta;
   double cdt, cdtv, cdtv2, cdtv3, dt1_init;

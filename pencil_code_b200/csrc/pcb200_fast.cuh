@@ -25,6 +25,24 @@ __device__ __forceinline__ double d5_line(const double m[3], const double p[3], 
   return cP.d5fac[dir] * (5.0 * (p[0] - m[0]) - 4.0 * (p[1] - m[1]) + (p[2] - m[2]));
 }
 
+// exp(x) for the equation of state: x = k ln2 + r, |r| <= ln2/2 (Cody-Waite, two-part ln2), degree-13
+// Taylor polynomial of exp(r) (truncation 4e-18 relative), coefficients read from constant memory as
+// FMA operands; 2^k by an integer add on the exponent field.  ~1 ulp for |x| < 700 (the EOS arguments
+// are O(1)); no special-case branches.  Half the instructions of the library exp, whose coefficients
+// are materialised by two moves each.
+__device__ __forceinline__ double exp_fast(double x) {
+  const double shifter = 6755399441055744.0; // 1.5 * 2^52: the low word of x*log2e + shifter is rint(x*log2e)
+  const double t = fma(x, 1.4426950408889634074, shifter);
+  const int k = __double2loint(t);
+  const double kd = t - shifter;
+  double r = fma(kd, -6.93147180369123816490e-01, x);
+  r = fma(kd, -1.90821492927058770002e-10, r);
+  double p = cP.expc[13];
+#pragma unroll
+  for (int n = 12; n >= 0; --n) p = fma(p, r, cP.expc[n]);
+  return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
+}
+
 // Policy adapter: global memory lines (lets variant-2 physics run on the variant-1 access path)
 struct GlobalLines {
   static constexpr bool TRAIL = false;
@@ -193,7 +211,7 @@ __device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, doub
       if (UPW) upw_s += au[j] * (P.d6upfac[T::dr(j)] * d6raw_line(ss, m, p));
     }
     const double e = P.cv1 * ss + P.gamma_m1 * (lnrho - P.lnrho0);
-    const double ex = exp(e);
+    const double ex = exp_fast(e);
     const double cs2 = P.cs20 * ex;
     const double TT1 = P.TT0_1 * __drcp_rn(ex); // = exp(-(lnTT0+e)) to 1 ulp, one exp less (eos_idealgas.f90:851-888)
     ho.TT1 = TT1;
@@ -297,7 +315,7 @@ template <bool ENT>
 __device__ __forceinline__ void combine_mag(const HydroOut &ho, const double jxb[3], double j2, double *__restrict__ rhs) {
   typedef Slots<ENT> S;
   const Pars &P = cP;
-  const double rho1 = exp(-ho.lnrho);
+  const double rho1 = exp_fast(-ho.lnrho);
   if (P.llorentzforce) {
 #pragma unroll
     for (int i = 0; i < 3; ++i) rhs[S::IUX + i] += rho1 * jxb[i];

@@ -38,11 +38,12 @@ template <bool ENT, bool MAG> struct V3Layout {
 };
 
 // tap policy on the v3 layout (same interface as SmemLines)
-template <bool ENT, bool MAG> struct V3Lines {
+template <bool ENT, bool MAG, bool ISO_ = false> struct V3Lines {
   typedef Slots<ENT> S;
   static constexpr bool TRAIL = false;
-  static __device__ __forceinline__ int dr(int j) { return j; }
-  static __device__ __forceinline__ int pr(int p) { return p; }
+  static constexpr bool ISO = ISO_; // dx == dy == dz: one set of stencil weights
+  static __device__ __forceinline__ int dr(int j) { return ISO ? 0 : j; }
+  static __device__ __forceinline__ int pr(int p) { return ISO ? 0 : p; }
   __device__ __forceinline__ void trail_pop(int, double *) {}
   __device__ __forceinline__ void trail_add(int, int, int, const double *, const double *) {}
   __device__ __forceinline__ void lead(int, double *) const {}
@@ -114,7 +115,7 @@ template <bool ENT, bool MAG> struct V3Lines {
         g[i] = (qp[a] - qp[-a]) + (qm[-a] - qm[a]);
       }
     }
-    return cP.dmc[pair][0] * g[0] + (cP.dmc[pair][1] * g[1] + cP.dmc[pair][2] * g[2]);
+    return cP.dmc[pr(pair)][0] * g[0] + (cP.dmc[pr(pair)][1] * g[1] + cP.dmc[pr(pair)][2] * g[2]);
   }
 };
 
@@ -125,7 +126,7 @@ extern __shared__ __align__(1024) double v3_smem[];
 // because a warp may run one plane ahead of the slowest one)
 enum { BAR_MBOX_FULL = 1, BAR_MBOX_FREE = 2, BAR_PLANE_EVEN = 3, BAR_PLANE_ODD = 4 };
 
-template <bool ENT, bool MAG, bool HYP, bool UPW>
+template <bool ENT, bool MAG, bool HYP, bool UPW, bool ISO = false>
 __global__ void __launch_bounds__((V3Layout<ENT, MAG>::THREADS), 1)
     rhs_update_v3(const __grid_constant__ CUtensorMap tmap_ring, const __grid_constant__ CUtensorMap tmap_scal, const V2Args a) {
   typedef V3Layout<ENT, MAG> L;
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__((V3Layout<ENT, MAG>::THREADS), 1)
     issue_scal(0);
   }
 
-  V3Lines<ENT, MAG> tp;
+  V3Lines<ENT, MAG, ISO> tp;
   const int toff = (ty + NG) * V3_HX + (tx + NG);
   const long long col = ixc + cP.sy * iyc;
   if (role == 0) {
@@ -232,7 +233,7 @@ __global__ void __launch_bounds__((V3Layout<ENT, MAG>::THREADS), 1)
       mbar_wait(&bar_scal[j0 & 1], (j0 >> 1) & 1);
       double rhs[NVH], fc[NVH];
       HydroOut ho;
-      if (active) hydro_part<ENT, HYP, UPW, V3Lines<ENT, MAG>, !MAG>(tp, rhs, fc, ho);
+      if (active) hydro_part<ENT, HYP, UPW, V3Lines<ENT, MAG, ISO>, !MAG>(tp, rhs, fc, ho);
       if (MAG) {
         named_bar_sync(BAR_MBOX_FULL, L::THREADS); // mailbox of this plane is full
         if (active) { // Lorentz force + (nu/3) mixed part of grad div u; Ohmic heating / TT1

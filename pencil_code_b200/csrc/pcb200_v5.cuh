@@ -1,84 +1,218 @@
-// pcb200_v5.cuh -- kernel variant 5: variant 4 (z-marching TMA ring, lead/trail z-mixed derivatives)
-// with the non-arithmetic instruction overhead removed.  Per cell and substep variant 4 executes
-// 1468 SASS instructions of which 693 are FP64 and 234 LDS.64; of the other 541, ~180 were 64-bit
-// address arithmetic for the 8+8+8+8 global accesses of df / f_out, 63 constant loads and ~50 register
-// moves.  Variant 5
-//   * walks the global arrays with per-thread running pointers (one 64-bit add per variable instead
-//     of an index multiply + scale per access),
-//   * issues the L2 prefetch of the df tile two planes ahead once per warp (lane -> variable, cache
-//     line) instead of once per cell and variable,
-//   * is instantiated for isotropic grids only (dx == dy == dz bit for bit, template flag ISO of the
-//     tap policy): one set of stencil weights serves all directions, 10 instead of 30 FP64 constants
-//     live in registers.  Anisotropic grids keep variant 4.
+// pcb200_v5.cuh -- kernel variant 5: the z-marching TMA ring with lead/trail z-mixed derivatives
+// (variant 4), restructured after the ncu source page of variant 4 (profiles/r01_v5_ncu_full_256.txt):
+//   * isotropic grids only (dx == dy == dz bit for bit): one set of stencil weights serves all
+//     directions, 10 instead of 30 FP64 constants; anisotropic grids keep variant 4;
+//   * running global pointers (one 64-bit add per variable instead of an index multiply + scale per
+//     access) and a warp-wide L2 prefetch of the df tile row (lane -> variable, cache line):
+//     1468 -> ~1290 SASS instructions per cell and substep;
+//   * the own-column value at z-3 of every ring field is carried in a register (it was loaded as the
+//     z-2 tap one plane earlier), so a ring slot is free one plane sooner: with the same 8 slots and
+//     3 scalar slots TMA now runs two planes ahead instead of one (7.5 % of the stall samples of the
+//     first version sat in mbarrier waits), and 6 LDS per cell disappear;
+//   * one TMA box per 3-vector (38 x 14 x 1 x 3) and one for {lnrho, ss}: the tighter padding pays for
+//     the third scalar slot (230.7 KB of the 227 KiB = 232448 B an sm_100a CTA may use).
 // Arithmetic and reference citations: pcb200_device.cuh / pcb200_fast.cuh.
 #pragma once
 #include "pcb200_fast.cuh"
 
 namespace pcb200 {
 
+constexpr int V5_GROUP = 1600; // 3 planes of 532 doubles = 12768 B -> 12800 B (TMA needs 128-byte aligned destinations)
+constexpr int V5_NSLOT = 8;    // ring: planes z-2..z+3 in use + 2 in flight
+constexpr int V5_NSCAL = 3;    // scalar planes: z in use + 2 in flight
+
+template <bool ENT, bool MAG> struct V5Layout {
+  static constexpr int NGROUP = MAG ? 2 : 1;
+  static constexpr int NSCAL = ENT ? 2 : 1;
+  static constexpr int SLOT = NGROUP * V5_GROUP;     // doubles per ring slot
+  static constexpr int RING_DOUBLES = V5_NSLOT * SLOT;
+  static constexpr int SCAL_SLOT = ENT ? 1072 : 544; // 8512 B -> 8576 B ; 4256 B -> 4352 B
+  static constexpr int SCAL_DOUBLES = V5_NSCAL * SCAL_SLOT;
+  static constexpr unsigned RING_TX_BYTES = NGROUP * 3 * V2_PLANE * 8;
+  static constexpr unsigned SCAL_TX_BYTES = NSCAL * V2_PLANE * 8;
+  static constexpr size_t SMEM_BYTES = (size_t)(RING_DOUBLES + SCAL_DOUBLES) * 8 + (V5_NSLOT + V5_NSCAL) * 8 + 64;
+};
+
+// tap policy (interface of SmemLines, pcb200_fast.cuh)
+template <bool ENT, bool MAG> struct RingLines5 {
+  typedef Slots<ENT> S;
+  static constexpr bool TRAIL = true, ISO = true;
+  static constexpr int NR = MAG ? 6 : 3;
+  static __device__ __forceinline__ int dr(int) { return 0; }
+  static __device__ __forceinline__ int pr(int) { return 0; }
+  const double *pl[6]; // planes z-2..z+3 of ring field u_x at this thread's cell (centre: pl[2])
+  const double *scal;  // current {lnrho, ss} planes at this thread's cell
+  double lz[7], sz[7]; // register pipelines of lnrho / ss along z
+  double zm3[NR];      // own-column values at z-3 of the ring fields
+  double T[MAG ? 2 : 1][3][3];
+
+  static __device__ __forceinline__ bool is_ring(int k) { return k < 3 || (MAG && k >= S::IAX); }
+  static __device__ __forceinline__ int ridx(int k) { return k < 3 ? k : 3 + (k - S::IAX); }
+  static __device__ __forceinline__ int foff(int k) { return k < 3 ? k * V2_PLANE : V5_GROUP + (k - S::IAX) * V2_PLANE; }
+  static __device__ __forceinline__ int goff(int g) { return g == 0 ? 0 : V5_GROUP; }
+
+  __device__ __forceinline__ void trail_zero() {
+#pragma unroll
+    for (int g = 0; g < (MAG ? 2 : 1); ++g)
+#pragma unroll
+      for (int c = 0; c < 3; ++c)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) T[g][c][j] = 0.0;
+  }
+  __device__ __forceinline__ void trail_pop(int g, double out[3]) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      out[c] = T[g][c][0];
+      T[g][c][0] = T[g][c][1];
+      T[g][c][1] = T[g][c][2];
+      T[g][c][2] = 0.0;
+    }
+  }
+  __device__ __forceinline__ void trail_add(int g, int c, int, const double m[3], const double p[3]) {
+#pragma unroll
+    for (int j = 0; j < 3; ++j) T[g][c][j] -= cP.dmc[0][j] * (p[j] - m[j]);
+  }
+  __device__ __forceinline__ void lead(int g, double out[3]) const {
+    const int fx = goff(g), fy = fx + V2_PLANE, fz = fy + V2_PLANE;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const double *q = pl[3 + j];
+      const int a = j + 1, b = (j + 1) * V2_HX;
+      out[0] += cP.dmc[0][j] * (q[fz + a] - q[fz - a]);
+      out[1] += cP.dmc[0][j] * (q[fz + b] - q[fz - b]);
+      out[2] += cP.dmc[0][j] * ((q[fx + a] - q[fx - a]) + (q[fy + b] - q[fy - b]));
+    }
+  }
+  // first plane of a z chunk: contributions of the planes z-3..z-1 (q3[0..2]) to the outputs z..z+2
+  __device__ __forceinline__ void trail_prologue(int g, const double *const q3[3]) {
+    const int fx = goff(g), fy = fx + V2_PLANE, fz = fy + V2_PLANE;
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      const double *q = q3[d];
+#pragma unroll
+      for (int k = 3 - d; k <= 3; ++k) {
+        const int j = d - 3 + k, a = k, b = k * V2_HX;
+        T[g][0][j] -= cP.dmc[0][k - 1] * (q[fz + a] - q[fz - a]);
+        T[g][1][j] -= cP.dmc[0][k - 1] * (q[fz + b] - q[fz - b]);
+        T[g][2][j] -= cP.dmc[0][k - 1] * ((q[fx + a] - q[fx - a]) + (q[fy + b] - q[fy - b]));
+      }
+    }
+  }
+
+  __device__ __forceinline__ double c(int k) const {
+    if (is_ring(k)) return pl[2][foff(k)];
+    return k == S::ILN ? lz[3] : sz[3];
+  }
+  __device__ __forceinline__ void line(int k, int dir, double m[3], double p[3]) {
+    if (is_ring(k)) {
+      const int f = foff(k);
+      if (dir == 2) {
+        m[0] = pl[1][f];
+        m[1] = pl[0][f];
+        m[2] = zm3[ridx(k)];
+        zm3[ridx(k)] = m[1]; // f(z-2) is the z-3 tap of the next plane
+#pragma unroll
+        for (int i = 0; i < 3; ++i) p[i] = pl[3 + i][f];
+      } else {
+        const double *q = pl[2] + f;
+        const int s = dir == 0 ? 1 : V2_HX;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          m[i] = q[-(i + 1) * s];
+          p[i] = q[(i + 1) * s];
+        }
+      }
+    } else {
+      if (dir == 2) {
+        const double *r = (k == S::ILN) ? lz : sz;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          m[i] = r[2 - i];
+          p[i] = r[4 + i];
+        }
+      } else {
+        const double *q = scal + (k == S::ILN ? 0 : V2_PLANE);
+        const int s = dir == 0 ? 1 : V2_HX;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          m[i] = q[-(i + 1) * s];
+          p[i] = q[(i + 1) * s];
+        }
+      }
+    }
+  }
+  // bidiagonal xy derivative in the centre plane (the z-mixed ones are lead + trail)
+  __device__ __forceinline__ double dij(int k, int) const {
+    const double *q = pl[2] + foff(k);
+    double g[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int a = (i + 1), b = (i + 1) * V2_HX;
+      g[i] = (q[a + b] - q[-a + b]) + (q[-a - b] - q[a - b]);
+    }
+    return cP.dmc[0][0] * g[0] + (cP.dmc[0][1] * g[1] + cP.dmc[0][2] * g[2]);
+  }
+};
+
+extern __shared__ __align__(1024) double v5_smem[];
+
 template <bool ENT, bool MAG, bool HYP, bool UPW>
 __global__ void __launch_bounds__(V2_THREADS, 1)
-    rhs_update_v5(const __grid_constant__ CUtensorMap tmap, const V2Args a) {
-  typedef V2Layout<ENT, MAG> L;
+    rhs_update_v5(const __grid_constant__ CUtensorMap tmap_ring, const __grid_constant__ CUtensorMap tmap_scal, const V2Args a) {
+  typedef V5Layout<ENT, MAG> L;
   typedef Slots<ENT> S;
   constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
-  double *ring = v2_smem;
+  double *ring = v5_smem;
   double *scal = ring + L::RING_DOUBLES;
   uint64_t *bar_ring = reinterpret_cast<uint64_t *>(scal + L::SCAL_DOUBLES);
-  uint64_t *bar_scal = bar_ring + V2_NSLOT;
+  uint64_t *bar_scal = bar_ring + V5_NSLOT;
 
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * V2_TX + tx;
-  const int bx0 = blockIdx.x * V2_TX, by0 = blockIdx.y * V2_TY;
+  const int bx0 = blockIdx.x * V2_TX, by0 = blockIdx.y * V2_TY; // origin of the halo'd tile (incl. ghosts)
   const int zc0 = a.z_lo + blockIdx.z * a.lz;
   const int zc1 = min(zc0 + a.lz, a.z_hi);
   if (zc0 >= zc1) return;
   const int ix = bx0 + tx + NG, iy = by0 + ty + NG;
   const bool active = ix < cP.nx + NG && iy < cP.ny + NG;
-  const int ixc = min(ix, cP.nx + NG - 1), iyc = min(iy, cP.ny + NG - 1);
+  const int ixc = min(ix, cP.nx + NG - 1), iyc = min(iy, cP.ny + NG - 1); // clamped (register pipelines)
   const int last_plane = zc1 - 1 + NG;
 
   if (tid == 0) {
     if (smem_u32(ring) & 127u) __trap();
-    for (int s = 0; s < V2_NSLOT; ++s) mbar_init(&bar_ring[s], 1);
-    mbar_init(&bar_scal[0], 1);
-    mbar_init(&bar_scal[1], 1);
+    for (int s = 0; s < V5_NSLOT + V5_NSCAL; ++s) mbar_init(&bar_ring[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   __syncthreads();
 
-  auto issue_ring = [&](int j) { // ring plane j <-> z = zc0-3+j
+  auto issue_ring = [&](int j) { // ring plane j <-> z = zc0-3+j, slot j % 8
     const int p = zc0 - NG + j;
     if (p > last_plane) return;
-    const int slot = j % V2_NSLOT;
-    mbar_expect_tx(&bar_ring[slot], L::NRING * V2_BOX_BYTES);
-#pragma unroll
-    for (int f = 0; f < L::NRING; ++f) {
-      const int var = f < 3 ? f : S::IAX + (f - 3);
-      tma_load_4d(ring + (slot * L::NRING + f) * V2_PLANE_PAD, &tmap, &bar_ring[slot], bx0, by0, p, var);
-    }
+    const int slot = j % V5_NSLOT;
+    mbar_expect_tx(&bar_ring[slot], L::RING_TX_BYTES);
+    tma_load_4d(ring + slot * L::SLOT, &tmap_ring, &bar_ring[slot], bx0, by0, p, S::IUX);
+    if (MAG) tma_load_4d(ring + slot * L::SLOT + V5_GROUP, &tmap_ring, &bar_ring[slot], bx0, by0, p, S::IAX);
   };
-  auto issue_scal = [&](int j) { // scalar plane j <-> z = zc0+j
+  auto issue_scal = [&](int j, int slot) { // scalar plane j <-> z = zc0+j, slot j % 3
     const int p = zc0 + j;
     if (p >= zc1) return;
-    const int slot = j & 1;
-    mbar_expect_tx(&bar_scal[slot], L::NSCAL * V2_BOX_BYTES);
-    tma_load_4d(scal + (slot * L::NSCAL + 0) * V2_PLANE_PAD, &tmap, &bar_scal[slot], bx0, by0, p, S::ILN);
-    if (ENT) tma_load_4d(scal + (slot * L::NSCAL + 1) * V2_PLANE_PAD, &tmap, &bar_scal[slot], bx0, by0, p, S::ISS);
+    mbar_expect_tx(&bar_scal[slot], L::SCAL_TX_BYTES);
+    tma_load_4d(scal + slot * L::SCAL_SLOT, &tmap_scal, &bar_scal[slot], bx0, by0, p, S::ILN);
   };
 
   if (tid == 0) {
 #pragma unroll 1
-    for (int j = 0; j < 7; ++j) issue_ring(j);
-    issue_scal(0);
+    for (int j = 0; j < V5_NSLOT; ++j) issue_ring(j);
+#pragma unroll 1
+    for (int j = 0; j < V5_NSCAL; ++j) issue_scal(j, j);
   }
 
-  SmemLines<ENT, MAG, true, true> tp;
+  RingLines5<ENT, MAG> tp;
   tp.trail_zero();
   const int toff = (ty + NG) * V2_HX + (tx + NG);
   const long long sv = cP.sv, sz = cP.sz;
   const long long col = ixc + cP.sy * iyc;
-  {
+  { // register pipelines of the scalars (own column, straight from global; coalesced)
     const double *gl = a.fin + col + S::ILN * sv + sz * (zc0 - NG);
 #pragma unroll
     for (int d = 0; d < 7; ++d) tp.lz[d] = __ldg(gl + sz * d);
@@ -92,22 +226,28 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
 
   // running pointers of this thread (all advance by one plane per iteration)
   const long long o0 = ix + cP.sy * iy + sz * zc0;
-  double *pdf = a.df + o0;                                         // df(ix,iy,z,0)
-  double *pfo = a.fout + o0;                                       // f_out(ix,iy,z,0)
-  const double *pnx = a.fin + col + S::ILN * sv + sz * (zc0 + 4);  // lnrho(ixc,iyc,z+4): next pipeline entry
+  double *pdf = a.df + o0;                                        // df(ix,iy,z,0)
+  double *pfo = a.fout + o0;                                      // f_out(ix,iy,z,0)
+  const double *pnx = a.fin + col + S::ILN * sv + sz * (zc0 + 4); // lnrho(ixc,iyc,z+4): next pipeline entry
   // warp-wide L2 prefetch of the df tile row two planes ahead: lane -> (variable, 128-byte line of the row)
   const int pf_k = tx / 3, pf_l = tx - 3 * pf_k;
   const bool pf_on = a.read_df != 0 && a.df_prefetch != 0 && pf_k < NV && iy < cP.ny + NG;
   const double *ppf = a.df + (bx0 + NG + min(pf_l * 16, V2_TX - 1)) + cP.sy * iyc + sz * (zc0 + 2) + pf_k * sv;
+  int sc_slot = 0, sc_par = 0; // slot and phase parity of the scalar plane of this iteration
 
 #pragma unroll 1
   for (int z = zc0; z < zc1; ++z) {
     const int j0 = z - zc0;
-    if (tid < 32) {
-      if (j0 > 0) named_bar_sync(1 + ((j0 - 1) & 1), V2_THREADS);
+    // slot release + TMA issue: the first warp waits until every warp has finished plane z-1, then refills the
+    // slots that plane freed.  Named barriers 1..4 rotate: with TMA two planes ahead a warp can arrive for
+    // planes z-1, z and z+1 before the slowest warp has arrived for z-1 (plane z+2 needs data that is only
+    // requested after the barrier of z-1 completed), so three generations can be open at once.
+    if (tid < 32 && j0 > 0) {
+      named_bar_sync(1 + ((j0 - 1) & 3), V2_THREADS);
       if (tid == 0) {
-        issue_ring(j0 + 7);
-        issue_scal(j0 + 1);
+        if (j0 == 1) issue_ring(V5_NSLOT); // slot 0 held plane z-3 of the first iteration (trail prologue)
+        issue_ring(j0 + V5_NSLOT);
+        issue_scal(j0 + 2, sc_slot == 0 ? 2 : sc_slot - 1);
       }
       __syncwarp();
     }
@@ -130,14 +270,18 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
 #pragma unroll 1
       for (int d = 0; d < 6; ++d) mbar_wait(&bar_ring[d], 0);
     }
-    mbar_wait(&bar_ring[(j0 + 6) % V2_NSLOT], ((j0 + 6) / V2_NSLOT) & 1);
-    mbar_wait(&bar_scal[j0 & 1], (j0 >> 1) & 1);
+    mbar_wait(&bar_ring[(j0 + 6) % V5_NSLOT], ((j0 + 6) / V5_NSLOT) & 1);
+    mbar_wait(&bar_scal[sc_slot], sc_par);
 #pragma unroll
-    for (int d = 0; d < 7; ++d) tp.pl[d] = ring + ((j0 + d) % V2_NSLOT) * (L::NRING * V2_PLANE_PAD) + toff;
-    tp.scal = scal + (j0 & 1) * (L::NSCAL * V2_PLANE_PAD) + toff;
+    for (int d = 0; d < 6; ++d) tp.pl[d] = ring + ((j0 + 1 + d) % V5_NSLOT) * L::SLOT + toff;
+    tp.scal = scal + sc_slot * L::SCAL_SLOT + toff;
     if (j0 == 0) {
-      tp.trail_prologue(0);
-      if (MAG) tp.trail_prologue(1);
+      const double *const q3[3] = {ring + toff, tp.pl[0], tp.pl[1]}; // planes z-3 (slot 0), z-2, z-1
+      tp.trail_prologue(0, q3);
+      if (MAG) tp.trail_prologue(1, q3);
+#pragma unroll
+      for (int r = 0; r < RingLines5<ENT, MAG>::NR; ++r)
+        tp.zm3[r] = q3[0][r < 3 ? r * V2_PLANE : V5_GROUP + (r - 3) * V2_PLANE];
     }
 
     if (active) {
@@ -163,6 +307,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
         qf += sv;
       }
     }
+    // advance the scalar pipelines and the running pointers
 #pragma unroll
     for (int d = 0; d < 6; ++d) {
       tp.lz[d] = tp.lz[d + 1];
@@ -174,7 +319,9 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     pfo += sz;
     pnx += sz;
     ppf += sz;
-    if (z + 1 < zc1 && tid >= 32) named_bar_arrive(1 + (j0 & 1), V2_THREADS);
+    if (++sc_slot == V5_NSCAL) { sc_slot = 0; sc_par ^= 1; }
+    // this warp is done with plane z-2's ring slot and with this scalar slot
+    if (z + 1 < zc1 && tid >= 32) named_bar_arrive(1 + (j0 & 3), V2_THREADS);
   }
 }
 
