@@ -111,10 +111,11 @@ def cpu_oracle_throughput(n, steps, nthreads=0):
 def run_reference(args, rank):
     """--impl reference: the reference's CPU implementation of the path.  The Fortran code cannot be
     compiled in this image (no gfortran/MPI), so this times the CPU oracle (restatement) with all host
-    threads on a bounded sample (128^3, same physics) of the workload."""
+    threads on a bounded sample (256^3, same physics; one step = one RK3 step of the sample, ~1 s on 16 cores)
+    of the workload."""
     if rank != 0:
         return
-    n = 128
+    n = 256
     per_step = []
     for _ in range(max(args.warmup, 0)):
         pass  # warm-up is inside cpu_oracle_throughput
@@ -287,9 +288,9 @@ def main():
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        v, el, cores = cpu_oracle_throughput(128, 2)
+        v, el, cores = cpu_oracle_throughput(256, 12)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": "128^3 periodic box, same 8-variable physics, 2 RK3 steps (%.1f s); CPU restatement "
+                        "sample": "256^3 periodic box, same 8-variable physics, 12 RK3 steps (%.1f s); CPU restatement "
                                   "(oracle) with g++ -O3 -march=native -fopenmp, not the Fortran binary" % el}
     if rank == 0:
         line = {

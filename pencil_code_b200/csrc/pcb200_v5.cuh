@@ -3,8 +3,8 @@
 //   * isotropic grids only (dx == dy == dz bit for bit): one set of stencil weights serves all
 //     directions, 10 instead of 30 FP64 constants; anisotropic grids keep variant 4;
 //   * running global pointers (one 64-bit add per variable instead of an index multiply + scale per
-//     access) and a warp-wide L2 prefetch of the df tile row (lane -> variable, cache line):
-//     1468 -> ~1290 SASS instructions per cell and substep;
+//     access); no L2 prefetch of df (with TMA two planes ahead it no longer pays) and plain read-only df
+//     loads: 1468 -> ~1270 SASS instructions per cell and substep;
 //   * the own-column value at z-3 of every ring field is carried in a register (it was loaded as the
 //     z-2 tap one plane earlier), so a ring slot is free one plane sooner: with the same 8 slots and
 //     3 scalar slots TMA now runs two planes ahead instead of one (7.5 % of the stall samples of the
@@ -229,10 +229,6 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
   double *pdf = a.df + o0;                                        // df(ix,iy,z,0)
   double *pfo = a.fout + o0;                                      // f_out(ix,iy,z,0)
   const double *pnx = a.fin + col + S::ILN * sv + sz * (zc0 + 4); // lnrho(ixc,iyc,z+4): next pipeline entry
-  // warp-wide L2 prefetch of the df tile row two planes ahead: lane -> (variable, 128-byte line of the row)
-  const int pf_k = tx / 3, pf_l = tx - 3 * pf_k;
-  const bool pf_on = a.read_df != 0 && a.df_prefetch != 0 && pf_k < NV && iy < cP.ny + NG;
-  const double *ppf = a.df + (bx0 + NG + min(pf_l * 16, V2_TX - 1)) + cP.sy * iyc + sz * (zc0 + 2) + pf_k * sv;
   int sc_slot = 0, sc_par = 0; // slot and phase parity of the scalar plane of this iteration
 
 #pragma unroll 1
@@ -256,11 +252,10 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
       const double *q = pdf;
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
-        dfv[k] = rdf ? __ldcs(q) : 0.0;
+        dfv[k] = rdf ? __ldg(q) : 0.0; // not ld.global.cs: evict-first lines were refetched (+6.7 GB DRAM reads in substep 3 at 512^3)
         q += sv;
       }
     }
-    if (pf_on && z + 2 < zc1) asm volatile("prefetch.global.L2 [%0];" ::"l"(ppf));
     double nl = 0.0, ns = 0.0;
     if (z + 4 < cP.mz) {
       nl = __ldg(pnx);
@@ -318,7 +313,6 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     pdf += sz;
     pfo += sz;
     pnx += sz;
-    ppf += sz;
     if (++sc_slot == V5_NSCAL) { sc_slot = 0; sc_par ^= 1; }
     // this warp is done with plane z-2's ring slot and with this scalar slot
     if (z + 1 < zc1 && tid >= 32) named_bar_arrive(1 + (j0 & 3), V2_THREADS);
