@@ -144,6 +144,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--kernel-variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--halo", default="p2p", choices=["p2p", "nccl"],
+                    help="z-halo transport: copy-engine puts into the neighbours' ghost planes (CUDA IPC) or NCCL send/recv")
     ap.add_argument("--decomp", default="slab", choices=["slab", "pencil"],
                     help="slab: 1x1xN z-slabs (config 3); pencil: squarest nprocy x nprocz yz-pencils (config 4)")
     args = ap.parse_args()
@@ -202,6 +204,10 @@ def main():
     g.L.pcb200_set_stream(stream.cuda_stream)
     g.register_GPU()
     g.initialize_GPU(fh, nt=0)
+    if world > 1 and args.halo == "p2p" and npz > 1:
+        blobs = [None] * world  # CUDA IPC handles of every rank's f buffers: z halos become copy-engine puts over NVLink
+        dist.all_gather_object(blobs, g.p2p_export())
+        g.p2p_connect(blobs)
     g.init_synthetic(12345)  # synthetic forced-turbulence-like state generated on the device
     g.synchronize()
 
@@ -284,6 +290,8 @@ def main():
         except Exception:
             pass
 
+    if world > 1:
+        barrier()  # nobody frees ghost planes a neighbour may still be writing to
     g.finalize_GPU()
 
     cpu_baseline = None
@@ -299,6 +307,7 @@ def main():
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": "periodic MHD with entropy %d^3 (8 vars, FP64), fixed dt, 2N-RK3" % n,
                        "decomposition": "1x%dx%d %s" % (npy, npz, "z-slabs" if npy == 1 else "yz-pencils"), "nvar": nvar,
+                       "z_halo": ("none (1 GPU)" if world == 1 else ("peer puts over NVLink (copy engines)" if args.halo == "p2p" and npz > 1 else "NCCL send/recv")),
                        "l2": "inputs larger than L2 (%.1f GB per f buffer per GPU)" % (nbytes_f / 1e9),
                        "kernel_variant": args.kernel_variant, "finite": finite},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes_f * world,

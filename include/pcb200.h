@@ -97,6 +97,14 @@ void pcb200_nccl_init(const char id[128], const int *rank, const int *nranks);
 
 /* use an externally owned CUDA stream (cudaStream_t as void*) for all work; NULL = own stream */
 void pcb200_set_stream(void *cuda_stream);
+/* z-halo exchange as copy-engine "puts" into the neighbours' ghost planes over NVLink peer memory (CUDA IPC),
+   replacing the NCCL send/recv pair (and with it mpicomm.f90:1544-2271 for the z direction) without using SMs:
+   every rank exports one blob after initialize_gpu_c, the host all-gathers them (MPI_Allgather in gpu_b200.f90)
+   and every rank connects with the table of all ranks' blobs (rank order).  Optional: without these calls the
+   z exchange runs on NCCL.  Ranks must not call finalize_gpu_c before all ranks have finished stepping. */
+int pcb200_p2p_blob_bytes(void);
+void pcb200_p2p_export(unsigned char *blob);
+void pcb200_p2p_connect(const unsigned char *blobs, const int *nranks);
 /* block until all queued device work has finished */
 void pcb200_synchronize(void);
 /* device-side synthetic initial condition written straight into the device f-array */

@@ -359,6 +359,16 @@ struct State {
   bool split = false;        // interior/boundary split of the fused kernel, z exchange overlapped
   int df_prefetch = 1;       // prefetch.global.L2 of df two planes ahead (+5 %); PCB200_DF_PREFETCH=0 disables
   bool loopback = false;     // test hook PCB200_LOOPBACK=1: exchange code path with self as every neighbour
+  // z-halo "put" over NVLink peer memory (copy engines, no SM): neighbours' f buffers and arrival counters are
+  // mapped through CUDA IPC; every exchange copies the boundary planes straight into the neighbour's ghost planes
+  // and then bumps the neighbour's counter, the receiver waits for the counter with a stream memory operation.
+  bool p2p = false;
+  double *peer_f[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}}; // [0 = lower (z-) neighbour, 1 = upper][buffer]
+  unsigned long long *flags = nullptr;                               // device: [0] written by the lower neighbour, [1] by the upper
+  unsigned long long *peer_flags[2] = {nullptr, nullptr};            // the neighbours' flag pairs
+  unsigned long long *seq_slots = nullptr;                           // device ring of sequence numbers (copy sources)
+  unsigned long long seq = 0;                                        // exchanges started so far (identical on all ranks)
+  std::vector<void *> ipc_opened;
   double *ybuf = nullptr;    // 4 staging buffers for y faces (send up/down, recv low/high)
   size_t ybuf_doubles = 0;
   // dt
@@ -640,7 +650,41 @@ static int rank_of(int ipy, int ipz) { // iproc = ipx + nprocx*(ipy + nprocy*ipz
 // (replaces initiate/finalize_isendrcv_bdry, mpicomm.f90:1544-2271; z-slabs are contiguous
 // plane ranges of an x-fastest array, so no packing is needed; the planes are mx*my wide and
 // therefore carry the x/y ghosts, i.e. the edges and corners)
+typedef CUresult (*PFN_streamValue64)(CUstream, CUdeviceptr, cuuint64_t, unsigned int);
+static PFN_streamValue64 drv_wait64 = nullptr, drv_write64 = nullptr;
+static void load_stream_memops() {
+  if (drv_wait64) return;
+  cudaDriverEntryPointQueryResult q;
+  void *fn = nullptr;
+  CK(cudaGetDriverEntryPoint("cuStreamWaitValue64", &fn, cudaEnableDefault, &q));
+  if (!fn || q != cudaDriverEntryPointSuccess) die("cuStreamWaitValue64 not available from the driver");
+  drv_wait64 = (PFN_streamValue64)fn;
+  CK(cudaGetDriverEntryPoint("cuStreamWriteValue64", &fn, cudaEnableDefault, &q));
+  if (!fn || q != cudaDriverEntryPointSuccess) die("cuStreamWriteValue64 not available from the driver");
+  drv_write64 = (PFN_streamValue64)fn;
+}
+
+// z-slab halo "put": my top 3 interior planes -> lower ghost planes of the upper neighbour, my bottom 3 interior
+// planes -> upper ghost planes of the lower neighbour (one contiguous copy per variable and side), then the arrival
+// counters.  Runs on copy engines over NVLink; the planes are mx*my wide (x/y ghosts included: edges, corners).
+static void put_z(double *f, cudaStream_t st) {
+  const Pars &P = S.P;
+  const int b = (f == S.f[0]) ? 0 : 1;
+  const size_t bytes = (size_t)NG * P.sz * sizeof(double);
+  for (int k = 0; k < P.nvar; ++k) { // contiguous plane ranges (a 2-D copy would hit cudaDeviceProp::memPitch on large slabs)
+    const size_t v = (size_t)k * P.sv;
+    CK(cudaMemcpyAsync(S.peer_f[1][b] + v, f + v + (size_t)P.nz * P.sz, bytes, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(S.peer_f[0][b] + v + (size_t)(NG + P.nz) * P.sz, f + v + (size_t)NG * P.sz, bytes, cudaMemcpyDeviceToDevice, st));
+  }
+  S.seq++;
+  unsigned long long *slot = S.seq_slots + (S.seq & 15);
+  if (drv_write64((CUstream)st, (CUdeviceptr)slot, (cuuint64_t)S.seq, 0) != CUDA_SUCCESS) die("cuStreamWriteValue64 failed");
+  CK(cudaMemcpyAsync(S.peer_flags[1] + 0, slot, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st)); // I am its lower neighbour
+  CK(cudaMemcpyAsync(S.peer_flags[0] + 1, slot, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st)); // I am its upper neighbour
+}
+
 static void exchange_z(double *f, cudaStream_t st) {
+  if (S.p2p) { put_z(f, st); return; }
   const Pars &P = S.P;
   const int up = rank_of(S.cfg.ipy, S.cfg.ipz + 1), dn = rank_of(S.cfg.ipy, S.cfg.ipz - 1);
   const size_t cnt = (size_t)NG * P.sz;
@@ -691,7 +735,12 @@ static void start_z_halo(double *f, cudaStream_t st) {
 // make stream st see the complete ghost zones of f[cur]
 static void wait_halo(cudaStream_t st) {
   if (!S.halo_pending) return;
-  CK(cudaStreamWaitEvent(st, S.ev_halo, 0));
+  CK(cudaStreamWaitEvent(st, S.ev_halo, 0)); // my own sends / puts have left
+  if (S.p2p) {                               // both neighbours' planes of this exchange have landed
+    for (int d = 0; d < 2; ++d)
+      if (drv_wait64((CUstream)st, (CUdeviceptr)(S.flags + d), (cuuint64_t)S.seq, CU_STREAM_WAIT_VALUE_GEQ) != CUDA_SUCCESS)
+        die("cuStreamWaitValue64 failed");
+  }
   S.halo_pending = false;
 }
 // make all ghost zones of buffer f valid (x wrap locally; y and z wrap or exchange), in stream order
@@ -888,6 +937,48 @@ extern "C" void pcb200_nccl_init(const char id[128], const int *rank, const int 
   NCK(nccl.CommInitRank(&S.comm, S.nranks, u, S.rank));
 }
 
+// P2P z-halo: each rank exports IPC handles of its two f buffers and of its arrival counters (3 x 64 bytes),
+// the host all-gathers the blobs (MPI_Allgather in gpu_b200.f90, torch.distributed in bench.py) and hands
+// the table of all ranks to pcb200_p2p_connect.  Without this call the z exchange stays on NCCL send/recv.
+extern "C" int pcb200_p2p_blob_bytes(void) { return 3 * (int)sizeof(cudaIpcMemHandle_t); }
+extern "C" void pcb200_p2p_export(unsigned char *blob) {
+  need_init("pcb200_p2p_export");
+  if (!S.flags) {
+    CK(cudaMalloc(&S.flags, 2 * sizeof(unsigned long long)));
+    CK(cudaMemset(S.flags, 0, 2 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&S.seq_slots, 16 * sizeof(unsigned long long)));
+    CK(cudaDeviceSynchronize());
+  }
+  cudaIpcMemHandle_t h[3];
+  CK(cudaIpcGetMemHandle(&h[0], S.f[0]));
+  CK(cudaIpcGetMemHandle(&h[1], S.f[1]));
+  CK(cudaIpcGetMemHandle(&h[2], S.flags));
+  std::memcpy(blob, h, sizeof(h));
+}
+extern "C" void pcb200_p2p_connect(const unsigned char *blobs, const int *nranks) {
+  need_init("pcb200_p2p_connect");
+  if (*nranks != S.nranks) die("pcb200_p2p_connect: %d blobs for %d ranks", *nranks, S.nranks);
+  if (S.cfg.nprocz < 2) return; // z is wrapped locally
+  if (!S.flags) die("pcb200_p2p_connect: call pcb200_p2p_export first");
+  load_stream_memops();
+  const int nb[2] = {rank_of(S.cfg.ipy, S.cfg.ipz - 1), rank_of(S.cfg.ipy, S.cfg.ipz + 1)};
+  for (int d = 0; d < 2; ++d) {
+    if (d == 1 && nb[1] == nb[0]) { // two slabs: the same neighbour on both sides
+      S.peer_f[1][0] = S.peer_f[0][0]; S.peer_f[1][1] = S.peer_f[0][1]; S.peer_flags[1] = S.peer_flags[0];
+      break;
+    }
+    cudaIpcMemHandle_t h[3];
+    std::memcpy(h, blobs + (size_t)nb[d] * sizeof(h), sizeof(h));
+    void *p[3];
+    for (int i = 0; i < 3; ++i) {
+      CK(cudaIpcOpenMemHandle(&p[i], h[i], cudaIpcMemLazyEnablePeerAccess));
+      S.ipc_opened.push_back(p[i]);
+    }
+    S.peer_f[d][0] = (double *)p[0]; S.peer_f[d][1] = (double *)p[1]; S.peer_flags[d] = (unsigned long long *)p[2];
+  }
+  S.p2p = true;
+}
+
 extern "C" void pcb200_set_stream(void *cuda_stream) {
   if (S.initialized) CK(cudaStreamSynchronize(S.stream));
   if (S.own_stream && S.stream) { CK(cudaStreamDestroy(S.stream)); S.own_stream = false; }
@@ -1006,10 +1097,16 @@ FTN_ALIAS(initialize_gpu_c)
 
 extern "C" void finalize_gpu_c(void) {
   if (!S.initialized) return;
+  if (S.p2p) { // both neighbours' last puts must have landed before the ghost planes they target are freed
+    for (int d = 0; d < 2; ++d) drv_wait64((CUstream)S.stream, (CUdeviceptr)(S.flags + d), (cuuint64_t)S.seq, CU_STREAM_WAIT_VALUE_GEQ);
+  }
   CK(cudaDeviceSynchronize());
   drain_timing();
   for (cudaEvent_t e : S.ev_pool) cudaEventDestroy(e);
   S.ev_pool.clear();
+  for (void *q : S.ipc_opened) cudaIpcCloseMemHandle(q);
+  S.ipc_opened.clear();
+  if (S.flags) { cudaFree(S.flags); cudaFree(S.seq_slots); }
   cudaFree(S.f[0]); cudaFree(S.f[1]); cudaFree(S.df);
   if (S.ybuf) cudaFree(S.ybuf);
   cudaFree(S.dt_dev); cudaFree(S.dt1_dev); cudaFree(S.partial); cudaFree(S.diag_dev); cudaFree(S.fx_dev);

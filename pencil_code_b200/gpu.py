@@ -61,6 +61,7 @@ ABI_SYMBOLS = (
     "pcb200_set_forcing_hel", "pcb200_request_diagnostics", "pcb200_nccl_get_unique_id", "pcb200_nccl_init",
     "pcb200_set_stream", "pcb200_synchronize", "pcb200_init_synthetic", "pcb200_launch_count",
     "pcb200_kernel_timing", "pcb200_enable_kernel_timing",
+    "pcb200_p2p_blob_bytes", "pcb200_p2p_export", "pcb200_p2p_connect",
     "initialize_gpu_c", "register_gpu_c", "finalize_gpu_c", "rhs_gpu_c", "before_boundary_gpu_c",
     "update_after_substep_gpu_c", "load_farray_c", "copy_farray_c", "gpu_prepare_for_first_substep_c",
     "get_farray_ptr_gpu_c", "reload_gpu_config_c", "update_on_gpu_scal_by_name_c", "update_on_gpu_vec_by_name_c",
@@ -94,6 +95,9 @@ def load_library():
     L.pcb200_nccl_get_unique_id.argtypes = [C.c_char_p]
     L.pcb200_nccl_init.argtypes = [C.c_char_p, ip, ip]
     L.pcb200_set_stream.argtypes = [C.c_void_p]
+    L.pcb200_p2p_blob_bytes.restype = C.c_int
+    L.pcb200_p2p_export.argtypes = [C.c_char_p]
+    L.pcb200_p2p_connect.argtypes = [C.c_char_p, ip]
     L.pcb200_init_synthetic.argtypes = [ip]
     L.pcb200_launch_count.restype = C.c_longlong
     L.pcb200_kernel_timing.argtypes = [dp, C.POINTER(C.c_longlong), ip]
@@ -166,6 +170,18 @@ class GPU:
         self.L.initialize_gpu_c(_dp(f), C.byref(comm), C.byref(ct), C.byref(cnt), C.byref(z), C.byref(z), C.byref(z))
         if nt > 0:
             self.load_farray_to_GPU(f)
+
+    # --- z-halo over NVLink peer memory (include/pcb200.h: pcb200_p2p_*) ---------
+    def p2p_export(self):
+        """IPC blob of this rank (call after initialize_GPU); all-gather the blobs of all ranks in rank order."""
+        buf = C.create_string_buffer(self.L.pcb200_p2p_blob_bytes())
+        self.L.pcb200_p2p_export(buf)
+        return bytes(buf.raw)
+
+    def p2p_connect(self, blobs):
+        """blobs: list of every rank's p2p_export() in rank order; switches the z exchange from NCCL to peer puts."""
+        table = b"".join(blobs)
+        self.L.pcb200_p2p_connect(table, C.byref(C.c_int(len(blobs))))
 
     def finalize_GPU(self):
         self.L.finalize_gpu_c()
