@@ -77,6 +77,19 @@ module GPU
       character(kind=c_char), dimension(128), intent(in) :: id
       integer(c_int), intent(in) :: rank, nranks
     endsubroutine
+    function pcb200_p2p_blob_bytes() bind(C,name="pcb200_p2p_blob_bytes") result(n)
+      import :: c_int
+      integer(c_int) :: n
+    endfunction
+    subroutine pcb200_p2p_export(blob) bind(C,name="pcb200_p2p_export")
+      import :: c_char
+      character(kind=c_char), dimension(*), intent(out) :: blob
+    endsubroutine
+    subroutine pcb200_p2p_connect(blobs,nranks) bind(C,name="pcb200_p2p_connect")
+      import :: c_char, c_int
+      character(kind=c_char), dimension(*), intent(in) :: blobs
+      integer(c_int), intent(in) :: nranks
+    endsubroutine
     subroutine pcb200_request_diagnostics() bind(C,name="pcb200_request_diagnostics")
     endsubroutine
     subroutine pcb200_push_forcing_c() bind(C,name="pcb200_push_forcing_c")
@@ -151,10 +164,11 @@ module GPU
   logical :: ltest_bcs=.false.     !PAR-DOC: accepted for namelist compatibility with gpu_astaroth
   logical :: ltest_rhs=.false.     !PAR-DOC: run test_rhs_gpu (equ.f90:1974-2143) at step it_test_rhs
   integer :: it_test_rhs=1
-  integer :: kernel_variant=0      !PAR-DOC: 0=auto, 1=global-load kernel, 2=shared-memory z-marching kernel
+  integer :: kernel_variant=0      !PAR-DOC: 0=auto (5 on isotropic grids, else 4; 1 for odd mx), 1=global-load kernel, 2-5=TMA z-marching kernels
   integer :: gpu_device=-1         !PAR-DOC: CUDA device; -1 = local rank modulo device count
 
-  namelist /gpu_run_pars/ ltest_bcs, ltest_rhs, it_test_rhs, kernel_variant, gpu_device
+  logical :: lp2p_halo=.true.      !PAR-DOC: z halos as peer-memory puts over NVLink (else NCCL send/recv)
+  namelist /gpu_run_pars/ ltest_bcs, ltest_rhs, it_test_rhs, kernel_variant, gpu_device, lp2p_halo
 
   type(pcb200_config), save :: cfg
 
@@ -246,10 +260,38 @@ contains
       if (dt<=0.) dt=dtmin
       zero=0
       call initialize_gpu_c(f,MPI_COMM_PENCIL,t,nt,zero,zero,zero)
+!
+!  z halos as copy-engine puts into the neighbours' ghost planes (NVLink peer memory): every rank exports
+!  the CUDA IPC handles of its device buffers, the table of all ranks is all-gathered over MPI.
+!  (All ranks of the run share one 8-GPU box; without this block the z exchange stays on NCCL.)
+!
+      if (ncpus>1 .and. nprocz>1 .and. lp2p_halo) call connect_p2p_halo
       if (nt>0) call load_farray_to_GPU(f)
       call get_farray_ptr_gpu
 
     endsubroutine initialize_GPU
+!***********************************************************************
+    subroutine connect_p2p_halo
+!
+!  MPI_Allgather of the per-rank IPC blobs (pcb200_p2p_export) -> pcb200_p2p_connect.
+!
+      use Mpicomm, only: MPI_COMM_PENCIL
+      include 'mpif.h'
+
+      character(kind=c_char), dimension(:), allocatable :: blob, table
+      integer(c_int) :: nb, nranks
+      integer :: ierr
+
+      nb=pcb200_p2p_blob_bytes()
+      allocate(blob(nb),table(nb*ncpus))
+      call pcb200_p2p_export(blob)
+      call MPI_ALLGATHER(blob,nb,MPI_CHARACTER,table,nb,MPI_CHARACTER,MPI_COMM_PENCIL,ierr)
+      if (ierr/=0) call fatal_error('connect_p2p_halo','MPI_ALLGATHER failed')
+      nranks=ncpus
+      call pcb200_p2p_connect(table,nranks)
+      deallocate(blob,table)
+
+    endsubroutine connect_p2p_halo
 !***********************************************************************
     subroutine read_gpu_run_pars(iomsg)
 
@@ -273,6 +315,11 @@ contains
 !***********************************************************************
     subroutine finalize_GPU
 
+      use Mpicomm, only: mpibarrier
+!
+!  No rank may free ghost planes that a neighbour is still writing to (p2p halo).
+!
+      call mpibarrier
       call finalize_gpu_c
 
     endsubroutine finalize_GPU
