@@ -217,8 +217,11 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    from pencil_code_b200.gpu import HelicalForcing
+    forcing = HelicalForcing(pcfg.kvectors())  # iforce='helical', force=0.07, relhel=1; same stream on every rank
+
     def step(t):
-        return g.time_step(fh, dt, False, t)
+        return g.time_step(fh, dt, False, t, forcing=forcing.draw(dt))
 
     t = 0.0
     for _ in range(args.warmup):
@@ -305,7 +308,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "periodic MHD with entropy %d^3 (8 vars, FP64), fixed dt, 2N-RK3" % n,
+            "config": {"workload": "periodic MHD with entropy %d^3 (8 vars, FP64), helical forcing, fixed dt, 2N-RK3" % n,
                        "decomposition": "1x%dx%d %s" % (npy, npz, "z-slabs" if npy == 1 else "yz-pencils"), "nvar": nvar,
                        "z_halo": ("none (1 GPU)" if world == 1 else ("peer puts over NVLink (copy engines)" if args.halo == "p2p" and npz > 1 else "NCCL send/recv")),
                        "l2": "inputs larger than L2 (%.1f GB per f buffer per GPU)" % (nbytes_f / 1e9),

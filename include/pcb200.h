@@ -85,6 +85,13 @@ void pcb200_set_forcing_hel(const int *lforce, const double coef1[3], const doub
                             const double fda[3], const double kk[3], const double *phase,
                             const double *fact, const double *k1_ff);
 
+/* host-side fconst_coefs_hel (forcing.f90:1773-2001, default branches: no shear, lscale_kvector_*=F,
+   old_forcing_evector=F, cs0eff=cs0) for drivers that do not have the Fortran forcing module
+   (pcb200_driver_run, bench.py); by value, not a Fortran binding */
+void pcb200_forcing_coefs_hel(double force, double relhel, double kav, double cs0eff, double dt, const double kvec[3],
+                              double phase, double phi, double coef1[3], double coef2[3], double fda[3], double kk[3],
+                              double *fact);
+
 /* ask for time-series diagnostics to be reduced during the next substep 1
    (ldiagnos=lfirst.and.lout, equ.f90:120) */
 void pcb200_request_diagnostics(void);

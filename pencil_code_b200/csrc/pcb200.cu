@@ -1072,6 +1072,15 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   // halo machinery: yz-pencils need y-face staging; z exchange is overlapped with the interior kernel
   const char *lb = std::getenv("PCB200_LOOPBACK"); // test hook: run the exchange code path on one GPU (self neighbour)
   S.loopback = lb && std::atoi(lb) != 0 && S.nranks == 1;
+  const char *lp = std::getenv("PCB200_LOOPBACK_P2P"); // test hook: the peer-put z halo with this rank as both neighbours
+  if (S.loopback && lp && std::atoi(lp) != 0) {
+    load_stream_memops();
+    CK(cudaMalloc(&S.flags, 2 * sizeof(unsigned long long)));
+    CK(cudaMemset(S.flags, 0, 2 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&S.seq_slots, 16 * sizeof(unsigned long long)));
+    for (int d = 0; d < 2; ++d) { S.peer_f[d][0] = S.f[0]; S.peer_f[d][1] = S.f[1]; S.peer_flags[d] = S.flags; }
+    S.p2p = true;
+  }
   if (S.cfg.nprocy > 1 || S.loopback) {
     S.ybuf_doubles = (size_t)NG * P.mx * P.nz * P.nvar;
     CK(cudaMalloc(&S.ybuf, 4 * S.ybuf_doubles * sizeof(double)));

@@ -230,6 +230,13 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
   double *pfo = a.fout + o0;                                      // f_out(ix,iy,z,0)
   const double *pnx = a.fin + col + S::ILN * sv + sz * (zc0 + 4); // lnrho(ixc,iyc,z+4): next pipeline entry
   int sc_slot = 0, sc_par = 0; // slot and phase parity of the scalar plane of this iteration
+  // helical forcing (substep 3 only): fx(x)*fy(y) is fixed for this thread, fz(z) is fetched at the top of each plane
+  double fxy_r = 0.0, fxy_i = 0.0;
+  if (a.frc.on) {
+    const double2 fx = a.frc.fx[ixc], fy = a.frc.fy[iyc];
+    fxy_r = fx.x * fy.x - fx.y * fy.y;
+    fxy_i = fx.x * fy.y + fx.y * fy.x;
+  }
 
 #pragma unroll 1
   for (int z = zc0; z < zc1; ++z) {
@@ -256,6 +263,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
         q += sv;
       }
     }
+    double2 fzv = make_double2(0.0, 0.0);
+    if (a.frc.on) fzv = __ldg(a.frc.fz + z);
     double nl = 0.0, ns = 0.0;
     if (z + 4 < cP.mz) {
       nl = __ldg(pnx);
@@ -283,10 +292,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
       double rhs[NV], fc[NV];
       rhs_cell_lines<ENT, MAG, HYP, UPW>(tp, rhs, fc);
       double force[3] = {0., 0., 0.};
-      if (a.frc.on) {
-        const double2 fx = a.frc.fx[ix], fy = a.frc.fy[iy], fz = a.frc.fz[z];
-        const double xr = fx.x * fy.x - fx.y * fy.y, xi = fx.x * fy.y + fx.y * fy.x;
-        const double re = xr * fz.x - xi * fz.y, im = xr * fz.y + xi * fz.x;
+      if (a.frc.on) { // forcing.f90:2170-2345
+        const double re = fxy_r * fzv.x - fxy_i * fzv.y, im = fxy_r * fzv.y + fxy_i * fzv.x;
 #pragma unroll
         for (int j = 0; j < 3; ++j) force[j] = a.frc.fda[j] * (a.frc.coef1[j] * re - a.frc.coef2[j] * im);
       }

@@ -58,7 +58,7 @@ class DriverState(C.Structure):
 # every symbol include/pcb200.h declares (checked by tests/test_abi.py on CPU)
 ABI_SYMBOLS = (
     "pcb200_configure", "pcb200_sizeof_config", "pcb200_set_dt", "pcb200_get_dt1_max", "pcb200_get_dt",
-    "pcb200_set_forcing_hel", "pcb200_request_diagnostics", "pcb200_nccl_get_unique_id", "pcb200_nccl_init",
+    "pcb200_set_forcing_hel", "pcb200_forcing_coefs_hel", "pcb200_request_diagnostics", "pcb200_nccl_get_unique_id", "pcb200_nccl_init",
     "pcb200_set_stream", "pcb200_synchronize", "pcb200_init_synthetic", "pcb200_launch_count",
     "pcb200_kernel_timing", "pcb200_enable_kernel_timing",
     "pcb200_p2p_blob_bytes", "pcb200_p2p_export", "pcb200_p2p_connect",
@@ -303,6 +303,47 @@ class GPU:
             t += ds * (dt * beta[itsub - 1])
             self.update_after_substep_gpu()
         return dt, t
+
+
+class HelicalForcing:
+    """Per-step helical forcing coefficients (forcing.f90:1773-2001 fconst_coefs_hel, draw order :1804-1811)
+    from the library's own host routine pcb200_forcing_coefs_hel and a splitmix64 stream (seed 2024,
+    force=0.07, relhel=1, all integer k with 4.5 <= |k| < 5.5)."""
+
+    class Coefs:
+        pass
+
+    def __init__(self, kvecs, force=0.07, relhel=1.0, seed=2024):
+        self.L = load_library()
+        dp = C.POINTER(C.c_double)
+        self.L.pcb200_forcing_coefs_hel.argtypes = [C.c_double] * 5 + [dp, C.c_double, C.c_double, dp, dp, dp, dp, dp]
+        self.kvecs, self.force, self.relhel = list(kvecs), force, relhel
+        self.kav = sum((k[0] ** 2 + k[1] ** 2 + k[2] ** 2) ** 0.5 for k in self.kvecs) / len(self.kvecs)
+        self.state = seed & 0xFFFFFFFFFFFFFFFF
+
+    def _uniform(self):
+        m = 0xFFFFFFFFFFFFFFFF
+        self.state = (self.state + 0x9E3779B97F4A7C15) & m
+        z = self.state
+        z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & m
+        z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & m
+        z ^= z >> 31
+        return (z >> 11) * (1.0 / 9007199254740992.0)
+
+    def draw(self, dt):
+        import math
+        f1, f2, f3 = self._uniform(), self._uniform(), self._uniform()
+        phase = math.pi * (2 * f1 - 1.0)
+        ik = int(len(self.kvecs) * (0.9999 * f2) + 1) - 1
+        phi = f3 * 2 * math.pi
+        a3 = C.c_double * 3
+        c1, c2, fda, kk, fact = a3(), a3(), a3(), a3(), C.c_double()
+        self.L.pcb200_forcing_coefs_hel(self.force, self.relhel, self.kav, 1.0, dt, a3(*self.kvecs[ik]), phase, phi,
+                                        c1, c2, fda, kk, C.byref(fact))
+        o = HelicalForcing.Coefs()
+        o.coef1, o.coef2, o.fda, o.kk = list(c1), list(c2), list(fda), list(kk)
+        o.phase, o.fact, o.k1_ff = phase, fact.value, 1.0
+        return o
 
 
 def nccl_unique_id():

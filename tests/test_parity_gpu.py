@@ -161,6 +161,24 @@ def test_zero_velocity_uniform_state_is_steady(oracle_mod):
     assert np.abs(f - f0).max() <= 1e-15
 
 
+@pytest.mark.parametrize("overlap", [True, False])
+def test_p2p_put_path_loopback(oracle_mod, monkeypatch, overlap):
+    """The peer-memory z halo on ONE GPU (PCB200_LOOPBACK_P2P=1: this rank is both neighbours): copy-engine puts
+    into the ghost planes, the arrival counters and the cuStreamWaitValue64 ordering of the boundary kernels must
+    reproduce the periodic single-domain result, Courant dt included."""
+    monkeypatch.setenv("PCB200_LOOPBACK", "1")
+    monkeypatch.setenv("PCB200_LOOPBACK_P2P", "1")
+    if not overlap:
+        monkeypatch.setenv("PCB200_NO_OVERLAP", "1")
+    cfg = pcfg.make_config(34, True, True, ny=10, nz=17, nu=5e-3, eta=4e-3, chi=3e-3, cdt=0.4, cdtv=0.3)
+    fg, fc, sg, sc, (dtg, dtc, tg, tc) = pu.run_both(cfg, oracle_mod, 4, dt=0.0, ldt=True, diag_every=2)
+    assert pu.rel_linf(fg, fc).max() <= 1e-11
+    assert abs(dtg - dtc) <= 1e-12 * dtc
+    for a, b in zip(sg, sc):
+        for k in ("urms", "brms", "jrms", "dtu"):
+            assert abs(a[k] - b[k]) <= 1e-11 * abs(b[k])
+
+
 @pytest.mark.parametrize("variant", [1, 2, 3, 4, 5])
 @pytest.mark.parametrize("overlap", [True, False])
 def test_exchange_code_path_loopback(oracle_mod, monkeypatch, variant, overlap):
