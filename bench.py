@@ -144,6 +144,9 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--kernel-variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="mhd_entropy", choices=["mhd_entropy", "iso_mhd", "hydro_hyper3"],
+                    help="mhd_entropy: BASELINE configs[2]/[3] (headline, default 512^3); iso_mhd: configs[1] (use --size 128); "
+                         "hydro_hyper3: configs[4] (use --size 256)")
     ap.add_argument("--halo", default="p2p", choices=["p2p", "nccl"],
                     help="z-halo transport: copy-engine puts into the neighbours' ghost planes (CUDA IPC) or NCCL send/recv")
     ap.add_argument("--decomp", default="slab", choices=["slab", "pencil"],
@@ -184,7 +187,16 @@ def main():
     n = args.n
     npy, npz = decomp.choose_decomposition(world, args.decomp)
     ipy, ipz = decomp.rank_position(rank, npy, npz)
-    cfg = pcfg.config_mhd_entropy(n, nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
+    if args.workload == "iso_mhd":
+        cfg = pcfg.make_config(n, entropy=False, magnetic=True, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3,
+                               nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
+        wname = "isothermal forced MHD turbulence %d^3 (lnrho, uu, aa: 7 vars, FP64)" % n
+    elif args.workload == "hydro_hyper3":
+        cfg = pcfg.config_hydro_hyper3(n, nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
+        wname = "hydro-only forced turbulence %d^3 with 6th-order hyperdiffusion (4 vars, FP64)" % n
+    else:
+        cfg = pcfg.config_mhd_entropy(n, nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
+        wname = "periodic MHD with entropy %d^3 (8 vars, FP64)" % n
     cfg["device"] = local_rank
     cfg["kernel_variant"] = args.kernel_variant
     nvar = cfg["nvar"]
@@ -287,7 +299,7 @@ def main():
                 "algorithmic_bytes_per_launch": bytes_per_launch, "peak_source": peak_src,
                 "frac_of_nominal_8TBs": achieved / 8000.0}
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(traffic_file):
+    if os.path.exists(traffic_file) and args.workload == "mhd_entropy" and n == 512 and world == 1:
         try:
             roofline["traffic"] = json.load(open(traffic_file)).get("dram_bytes_per_launch_512")
         except Exception:
@@ -298,7 +310,7 @@ def main():
     g.finalize_GPU()
 
     cpu_baseline = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "mhd_entropy":
         v, el, cores = cpu_oracle_throughput(256, 12)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                         "sample": "256^3 periodic box, same 8-variable physics, 12 RK3 steps (%.1f s); CPU restatement "
@@ -308,7 +320,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "periodic MHD with entropy %d^3 (8 vars, FP64), helical forcing, fixed dt, 2N-RK3" % n,
+            "config": {"workload": wname + ", helical forcing, fixed dt, 2N-RK3",
                        "decomposition": "1x%dx%d %s" % (npy, npz, "z-slabs" if npy == 1 else "yz-pencils"), "nvar": nvar,
                        "z_halo": ("none (1 GPU)" if world == 1 else ("peer puts over NVLink (copy engines)" if args.halo == "p2p" and npz > 1 else "NCCL send/recv")),
                        "l2": "inputs larger than L2 (%.1f GB per f buffer per GPU)" % (nbytes_f / 1e9),
