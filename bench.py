@@ -311,9 +311,9 @@ def main():
 
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "mhd_entropy":
-        v, el, cores = cpu_oracle_throughput(256, 12)
+        v, el, cores = cpu_oracle_throughput(256, 16)
         cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": "256^3 periodic box, same 8-variable physics, 12 RK3 steps (%.1f s); CPU restatement "
+                        "sample": "256^3 periodic box, same 8-variable physics, 16 RK3 steps (%.1f s); CPU restatement "
                                   "(oracle) with g++ -O3 -march=native -fopenmp, not the Fortran binary" % el}
     if rank == 0:
         line = {
