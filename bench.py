@@ -219,7 +219,12 @@ def main():
     if world > 1 and args.halo == "p2p" and npz > 1:
         blobs = [None] * world  # CUDA IPC handles of every rank's f buffers: z halos become copy-engine puts over NVLink
         dist.all_gather_object(blobs, g.p2p_export())
-        g.p2p_connect(blobs)
+        ok = torch.tensor([1 if g.p2p_connect(blobs) else 0], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 1:
+            g.p2p_enable()
+        else:
+            args.halo = "nccl"  # some rank cannot map its neighbour (GPU not visible to the process): all ranks stay on NCCL
     g.init_synthetic(12345)  # synthetic forced-turbulence-like state generated on the device
     g.synchronize()
 

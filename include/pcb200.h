@@ -111,7 +111,10 @@ void pcb200_set_stream(void *cuda_stream);
    z exchange runs on NCCL.  Ranks must not call finalize_gpu_c before all ranks have finished stepping. */
 int pcb200_p2p_blob_bytes(void);
 void pcb200_p2p_export(unsigned char *blob);
-void pcb200_p2p_connect(const unsigned char *blobs, const int *nranks);
+/* returns 0 when both z neighbours' buffers are mapped, 1 when they cannot be (peer GPU not visible, no P2P) */
+int pcb200_p2p_connect(const unsigned char *blobs, const int *nranks);
+/* call on all ranks after every rank's connect returned 0 (the host reduces the status: MPI_ALLREDUCE / all_reduce) */
+void pcb200_p2p_enable(void);
 /* block until all queued device work has finished */
 void pcb200_synchronize(void);
 /* device-side synthetic initial condition written straight into the device f-array */

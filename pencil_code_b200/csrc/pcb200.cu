@@ -1018,10 +1018,10 @@ extern "C" void pcb200_p2p_export(unsigned char *blob) {
   CK(cudaIpcGetMemHandle(&h[2], S.flags));
   std::memcpy(blob, h, sizeof(h));
 }
-extern "C" void pcb200_p2p_connect(const unsigned char *blobs, const int *nranks) {
+extern "C" int pcb200_p2p_connect(const unsigned char *blobs, const int *nranks) {
   need_init("pcb200_p2p_connect");
   if (*nranks != S.nranks) die("pcb200_p2p_connect: %d blobs for %d ranks", *nranks, S.nranks);
-  if (S.cfg.nprocz < 2) return; // z is wrapped locally
+  if (S.cfg.nprocz < 2) return 0; // z is wrapped locally
   if (!S.flags) die("pcb200_p2p_connect: call pcb200_p2p_export first");
   load_stream_memops();
   const int nb[2] = {rank_of(S.cfg.ipy, S.cfg.ipz - 1), rank_of(S.cfg.ipy, S.cfg.ipz + 1)};
@@ -1034,11 +1034,25 @@ extern "C" void pcb200_p2p_connect(const unsigned char *blobs, const int *nranks
     std::memcpy(h, blobs + (size_t)nb[d] * sizeof(h), sizeof(h));
     void *p[3];
     for (int i = 0; i < 3; ++i) {
-      CK(cudaIpcOpenMemHandle(&p[i], h[i], cudaIpcMemLazyEnablePeerAccess));
+      const cudaError_t e = cudaIpcOpenMemHandle(&p[i], h[i], cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess) { // e.g. the neighbour's GPU is not visible to this process: the caller keeps NCCL
+        std::fprintf(stderr, "pcb200: rank %d cannot map rank %d's buffers (%s); z halo stays on NCCL\n", S.rank, nb[d], cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return 1;
+      }
       S.ipc_opened.push_back(p[i]);
     }
     S.peer_f[d][0] = (double *)p[0]; S.peer_f[d][1] = (double *)p[1]; S.peer_flags[d] = (unsigned long long *)p[2];
   }
+  return 0;
+}
+// switch the z halo to peer puts; call on ALL ranks, and only after every rank's pcb200_p2p_connect returned 0
+extern "C" void pcb200_p2p_enable(void) {
+  need_init("pcb200_p2p_enable");
+  if (S.cfg.nprocz < 2) return;
+  if (!S.peer_f[0][0] || !S.peer_f[1][0]) die("pcb200_p2p_enable: not connected");
+  wait_halo(S.stream); // an exchange started on the NCCL path finishes there
+  CK(cudaStreamSynchronize(S.stream));
   S.p2p = true;
 }
 

@@ -85,10 +85,13 @@ module GPU
       import :: c_char
       character(kind=c_char), dimension(*), intent(out) :: blob
     endsubroutine
-    subroutine pcb200_p2p_connect(blobs,nranks) bind(C,name="pcb200_p2p_connect")
+    function pcb200_p2p_connect(blobs,nranks) bind(C,name="pcb200_p2p_connect") result(ierr)
       import :: c_char, c_int
       character(kind=c_char), dimension(*), intent(in) :: blobs
       integer(c_int), intent(in) :: nranks
+      integer(c_int) :: ierr
+    endfunction
+    subroutine pcb200_p2p_enable() bind(C,name="pcb200_p2p_enable")
     endsubroutine
     subroutine pcb200_request_diagnostics() bind(C,name="pcb200_request_diagnostics")
     endsubroutine
@@ -280,7 +283,7 @@ contains
 
       character(kind=c_char), dimension(:), allocatable :: blob, table
       integer(c_int) :: nb, nranks
-      integer :: ierr
+      integer :: ierr, lfail, lfail_any
 
       nb=pcb200_p2p_blob_bytes()
       allocate(blob(nb),table(nb*ncpus))
@@ -288,7 +291,16 @@ contains
       call MPI_ALLGATHER(blob,nb,MPI_CHARACTER,table,nb,MPI_CHARACTER,MPI_COMM_PENCIL,ierr)
       if (ierr/=0) call fatal_error('connect_p2p_halo','MPI_ALLGATHER failed')
       nranks=ncpus
-      call pcb200_p2p_connect(table,nranks)
+      lfail=pcb200_p2p_connect(table,nranks)
+!
+!  All ranks switch together, or none does (a rank that cannot map its neighbour keeps everybody on NCCL).
+!
+      call MPI_ALLREDUCE(lfail,lfail_any,1,MPI_INTEGER,MPI_MAX,MPI_COMM_PENCIL,ierr)
+      if (lfail_any==0) then
+        call pcb200_p2p_enable
+      elseif (lroot) then
+        call warning('connect_p2p_halo','peer mapping failed on some rank; z halo stays on NCCL')
+      endif
       deallocate(blob,table)
 
     endsubroutine connect_p2p_halo

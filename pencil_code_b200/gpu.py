@@ -61,7 +61,7 @@ ABI_SYMBOLS = (
     "pcb200_set_forcing_hel", "pcb200_forcing_coefs_hel", "pcb200_request_diagnostics", "pcb200_nccl_get_unique_id", "pcb200_nccl_init",
     "pcb200_set_stream", "pcb200_synchronize", "pcb200_init_synthetic", "pcb200_launch_count",
     "pcb200_kernel_timing", "pcb200_enable_kernel_timing",
-    "pcb200_p2p_blob_bytes", "pcb200_p2p_export", "pcb200_p2p_connect",
+    "pcb200_p2p_blob_bytes", "pcb200_p2p_export", "pcb200_p2p_connect", "pcb200_p2p_enable",
     "initialize_gpu_c", "register_gpu_c", "finalize_gpu_c", "rhs_gpu_c", "before_boundary_gpu_c",
     "update_after_substep_gpu_c", "load_farray_c", "copy_farray_c", "gpu_prepare_for_first_substep_c",
     "get_farray_ptr_gpu_c", "reload_gpu_config_c", "update_on_gpu_scal_by_name_c", "update_on_gpu_vec_by_name_c",
@@ -98,6 +98,7 @@ def load_library():
     L.pcb200_p2p_blob_bytes.restype = C.c_int
     L.pcb200_p2p_export.argtypes = [C.c_char_p]
     L.pcb200_p2p_connect.argtypes = [C.c_char_p, ip]
+    L.pcb200_p2p_connect.restype = C.c_int
     L.pcb200_init_synthetic.argtypes = [ip]
     L.pcb200_launch_count.restype = C.c_longlong
     L.pcb200_kernel_timing.argtypes = [dp, C.POINTER(C.c_longlong), ip]
@@ -179,9 +180,14 @@ class GPU:
         return bytes(buf.raw)
 
     def p2p_connect(self, blobs):
-        """blobs: list of every rank's p2p_export() in rank order; switches the z exchange from NCCL to peer puts."""
+        """blobs: list of every rank's p2p_export() in rank order.  Returns True when this rank mapped both z
+        neighbours; the caller reduces the result over all ranks and then calls p2p_enable() on all of them."""
         table = b"".join(blobs)
-        self.L.pcb200_p2p_connect(table, C.byref(C.c_int(len(blobs))))
+        return self.L.pcb200_p2p_connect(table, C.byref(C.c_int(len(blobs)))) == 0
+
+    def p2p_enable(self):
+        """switch the z exchange from NCCL to peer puts (all ranks, after all of them connected)"""
+        self.L.pcb200_p2p_enable()
 
     def finalize_GPU(self):
         self.L.finalize_gpu_c()

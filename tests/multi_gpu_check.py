@@ -34,7 +34,10 @@ def run_case(rank, world, npy, npz, variant, ldt, p2p, nsteps=3):
     if p2p and npz > 1:  # z halos as copy-engine puts into the neighbours' ghost planes (CUDA IPC) instead of NCCL
         blobs = [None] * world
         dist.all_gather_object(blobs, g.p2p_export())
-        g.p2p_connect(blobs)
+        oks = [None] * world
+        dist.all_gather_object(oks, g.p2p_connect(blobs))
+        assert all(oks), "peer mapping failed on some rank: %s" % oks
+        g.p2p_enable()
     dt, t = (0.0 if ldt else pcfg.fixed_dt(gcfg)), 0.0
     series = []
     for s in range(nsteps):
