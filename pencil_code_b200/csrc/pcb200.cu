@@ -564,11 +564,11 @@ template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false> static voi
   rhs_update_v2<ENT, MAG, HYP, UPW, TRAIL><<<g, b, L::SMEM_BYTES, st>>>(tm, S.tmap_df, v);
 }
 
-template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v5(const UpdateArgs &a, cudaStream_t st) {
+template <bool ENT, bool MAG, bool HYP, bool UPW, bool TM = false> static void launch_update_v5(const UpdateArgs &a, cudaStream_t st) {
   typedef V5Layout<ENT, MAG> L;
   static bool attr_set = false;
   if (!attr_set) {
-    CK(cudaFuncSetAttribute(rhs_update_v5<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    CK(cudaFuncSetAttribute(rhs_update_v5<ENT, MAG, HYP, UPW, TM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
     attr_set = true;
   }
   V2Args v;
@@ -583,7 +583,7 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v5(c
   nch = (nzr + v.lz - 1) / v.lz;
   dim3 g(gx, gy, nch), b(V2_TX, V2_TY, 1);
   const int w = (a.fin == S.f[0]) ? 0 : 1;
-  rhs_update_v5<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(S.tmap3_ring[w], S.tmap3_scal[w], v);
+  rhs_update_v5<ENT, MAG, HYP, UPW, TM><<<g, b, L::SMEM_BYTES, st>>>(S.tmap3_ring[w], S.tmap3_scal[w], v);
 }
 
 template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v3(const UpdateArgs &a, cudaStream_t st) {
@@ -626,7 +626,8 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   }
 #define DISPATCH(E, M, H, U)                                   \
   do {                                                         \
-    if (S.variant == 5) launch_update_v5<E, M, H, U>(a, st);   \
+    if (S.variant == 6) launch_update_v5<E, M, H, U, true>(a, st); \
+    else if (S.variant == 5) launch_update_v5<E, M, H, U>(a, st);   \
     else if (S.variant == 4) launch_update_v2<E, M, H, U, true>(a, st); \
     else if (S.variant == 3) launch_update_v3<E, M, H, U>(a, st);   \
     else if (S.variant == 2) launch_update_v2<E, M, H, U>(a, st); \
@@ -1130,17 +1131,17 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   // kernel variant: TMA needs 16-byte global strides -> mx even
   const bool tma_ok = (P.mx % 2 == 0);
   const int kv = S.cfg.kernel_variant;
-  if (kv < 0 || kv > 5) die("kernel_variant=%d unknown (0 = auto, 1 ... 5)", kv);
+  if (kv < 0 || kv > 6) die("kernel_variant=%d unknown (0 = auto, 1 ... 6)", kv);
   if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
   const bool iso = S.cfg.dx == S.cfg.dy && S.cfg.dy == S.cfg.dz; // variant 5 shares one set of stencil weights
   S.variant = kv ? kv : (tma_ok ? (iso ? 5 : 4) : 1);
-  if (S.variant == 5 && !iso) S.variant = 4; // anisotropic spacing: same kernel structure with per-direction weights
+  if (S.variant >= 5 && !iso) S.variant = 4; // anisotropic spacing: same kernel structure with per-direction weights
   if (S.variant >= 2) make_tensor_map(&S.tmap_df, S.df, V2_TX, V2_TY, P.nvar);
   if (S.variant == 2 || S.variant == 4) {
     make_tensor_map(&S.tmap[0], S.f[0]);
     make_tensor_map(&S.tmap[1], S.f[1]);
   }
-  if (S.variant == 3 || S.variant == 5) {
+  if (S.variant == 3 || S.variant >= 5) {
     for (int w = 0; w < 2; ++w) {
       make_tensor_map(&S.tmap3_ring[w], S.f[w], V3_HX, V3_HY, 3);
       make_tensor_map(&S.tmap3_scal[w], S.f[w], V3_HX, V3_HY, S.cfg.iss >= 0 ? 2 : 1);

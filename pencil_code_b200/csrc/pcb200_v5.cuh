@@ -33,9 +33,32 @@ template <bool ENT, bool MAG> struct V5Layout {
   static constexpr size_t SMEM_BYTES = (size_t)(RING_DOUBLES + SCAL_DOUBLES) * 8 + (V5_NSLOT + V5_NSCAL) * 8 + 64;
 };
 
-// tap policy (interface of SmemLines, pcb200_fast.cuh)
-template <bool ENT, bool MAG> struct RingLines5 {
+// ---- tensor memory (TMEM) as per-thread scratch: tcgen05.ld/st, shape 32x32b (lane = thread, 32-bit columns)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t r[16]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                 "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+               : "r"(taddr));
+  // the registers are only valid after the wait: passing them through it orders every use behind it
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
+                 "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])::"memory");
+}
+__device__ __forceinline__ void tmem_st2d(uint32_t taddr, double a, double b) { // 2 doubles = 4 columns
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(__double2loint(a)),
+               "r"(__double2hiint(a)), "r"(__double2loint(b)), "r"(__double2hiint(b))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_st1d(uint32_t taddr, double a) { // 1 double = 2 columns
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(__double2loint(a)), "r"(__double2hiint(a)) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// tap policy (interface of SmemLines, pcb200_fast.cuh).  TM: the z histories of lnrho / ss live in TMEM (8 doubles =
+// 16 columns per variable and thread, entries f(z-3..z+3) + 1 spare) instead of two 7-deep register pipelines.
+template <bool ENT, bool MAG, bool TM = false> struct RingLines5 {
   typedef Slots<ENT> S;
+  uint32_t tm; // TMEM address (lane base of the warp, first column) of this thread's lnrho history; ss at +16
   static constexpr bool TRAIL = true, ISO = true;
   static constexpr int NR = MAG ? 6 : 3;
   static __device__ __forceinline__ int dr(int) { return 0; }
@@ -101,7 +124,26 @@ template <bool ENT, bool MAG> struct RingLines5 {
 
   __device__ __forceinline__ double c(int k) const {
     if (is_ring(k)) return pl[2][foff(k)];
+    if (TM) return scal[k == S::ILN ? 0 : V2_PLANE];
     return k == S::ILN ? lz[3] : sz[3];
+  }
+  // TMEM history of a scalar: taps of this plane, and the history shifted by one plane written back
+  // (entry 6 = f(z+4) follows at the end of the iteration, when the global load has landed)
+  __device__ __forceinline__ void tm_zline(int k, double m[3], double p[3]) {
+    const uint32_t a = tm + (k == S::ILN ? 0 : 16);
+    uint32_t r[16];
+    tmem_ld16(a, r);
+    double h[7];
+#pragma unroll
+    for (int i = 0; i < 7; ++i) h[i] = __hiloint2double((int)r[2 * i + 1], (int)r[2 * i]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      m[i] = h[2 - i];
+      p[i] = h[4 + i];
+    }
+    tmem_st2d(a + 0, h[1], h[2]);
+    tmem_st2d(a + 4, h[3], h[4]);
+    tmem_st2d(a + 8, h[5], h[6]);
   }
   __device__ __forceinline__ void line(int k, int dir, double m[3], double p[3]) {
     if (is_ring(k)) {
@@ -124,11 +166,15 @@ template <bool ENT, bool MAG> struct RingLines5 {
       }
     } else {
       if (dir == 2) {
-        const double *r = (k == S::ILN) ? lz : sz;
+        if (TM) {
+          tm_zline(k, m, p);
+        } else {
+          const double *r = (k == S::ILN) ? lz : sz;
 #pragma unroll
-        for (int i = 0; i < 3; ++i) {
-          m[i] = r[2 - i];
-          p[i] = r[4 + i];
+          for (int i = 0; i < 3; ++i) {
+            m[i] = r[2 - i];
+            p[i] = r[4 + i];
+          }
         }
       } else {
         const double *q = scal + (k == S::ILN ? 0 : V2_PLANE);
@@ -156,7 +202,7 @@ template <bool ENT, bool MAG> struct RingLines5 {
 
 extern __shared__ __align__(1024) double v5_smem[];
 
-template <bool ENT, bool MAG, bool HYP, bool UPW>
+template <bool ENT, bool MAG, bool HYP, bool UPW, bool TM = false>
 __global__ void __launch_bounds__(V2_THREADS, 1)
     rhs_update_v5(const __grid_constant__ CUtensorMap tmap_ring, const __grid_constant__ CUtensorMap tmap_scal, const V2Args a) {
   typedef V5Layout<ENT, MAG> L;
@@ -183,7 +229,16 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
+  uint32_t *tm_slot = reinterpret_cast<uint32_t *>(bar_scal + V5_NSCAL);
+  if (TM) { // 64 TMEM columns: 2 variables x 16 columns per thread, two warps share each lane quarter
+    if (tid < 32) {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_u32(tm_slot)) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  }
   __syncthreads();
+  if (TM) asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
   auto issue_ring = [&](int j) { // ring plane j <-> z = zc0-3+j, slot j % 8
     const int p = zc0 - NG + j;
@@ -207,18 +262,31 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     for (int j = 0; j < V5_NSCAL; ++j) issue_scal(j, j);
   }
 
-  RingLines5<ENT, MAG> tp;
+  RingLines5<ENT, MAG, TM> tp;
   tp.trail_zero();
+  if (TM) tp.tm = *tm_slot + ((uint32_t)((tid >> 5) & 3) << 21) + (uint32_t)(tid >> 7) * 32; // lane (warp%4)*32, column (warp/4)*32
   const int toff = (ty + NG) * V2_HX + (tx + NG);
   const long long sv = cP.sv, sz = cP.sz;
   const long long col = ixc + cP.sy * iyc;
   { // register pipelines of the scalars (own column, straight from global; coalesced)
     const double *gl = a.fin + col + S::ILN * sv + sz * (zc0 - NG);
+    if (TM) {
 #pragma unroll
-    for (int d = 0; d < 7; ++d) tp.lz[d] = __ldg(gl + sz * d);
-    if (ENT) {
+      for (int v = 0; v < (ENT ? 2 : 1); ++v) {
+        double h[8];
 #pragma unroll
-      for (int d = 0; d < 7; ++d) tp.sz[d] = __ldg(gl + sv + sz * d);
+        for (int d = 0; d < 7; ++d) h[d] = __ldg(gl + v * sv + sz * d);
+        h[7] = 0.0;
+#pragma unroll
+        for (int d = 0; d < 4; ++d) tmem_st2d(tp.tm + 16 * v + 4 * d, h[2 * d], h[2 * d + 1]);
+      }
+    } else {
+#pragma unroll
+      for (int d = 0; d < 7; ++d) tp.lz[d] = __ldg(gl + sz * d);
+      if (ENT) {
+#pragma unroll
+        for (int d = 0; d < 7; ++d) tp.sz[d] = __ldg(gl + sv + sz * d);
+      }
     }
   }
   const double dtb = (*a.dt_dev) * a.beta;
@@ -288,9 +356,13 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
         tp.zm3[r] = q3[0][r < 3 ? r * V2_PLANE : V5_GROUP + (r - 3) * V2_PLANE];
     }
 
+    if (TM) tmem_wait_st(); // the history stores of the previous plane (or of the prologue) are complete
+    double rhs[NV], fc[NV];
+    // TM: every thread evaluates the cell (tcgen05.ld/st are warp-collective; threads outside the grid work on
+    // zero-filled TMA data and store nothing)
+    if (TM) rhs_cell_lines<ENT, MAG, HYP, UPW>(tp, rhs, fc);
     if (active) {
-      double rhs[NV], fc[NV];
-      rhs_cell_lines<ENT, MAG, HYP, UPW>(tp, rhs, fc);
+      if (!TM) rhs_cell_lines<ENT, MAG, HYP, UPW>(tp, rhs, fc);
       double force[3] = {0., 0., 0.};
       if (a.frc.on) { // forcing.f90:2170-2345
         const double re = fxy_r * fzv.x - fxy_i * fzv.y, im = fxy_r * fzv.y + fxy_i * fzv.x;
@@ -310,19 +382,30 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
       }
     }
     // advance the scalar pipelines and the running pointers
+    if (TM) {
+      tmem_st1d(tp.tm + 12, nl);
+      if (ENT) tmem_st1d(tp.tm + 16 + 12, ns);
+    } else {
 #pragma unroll
-    for (int d = 0; d < 6; ++d) {
-      tp.lz[d] = tp.lz[d + 1];
-      if (ENT) tp.sz[d] = tp.sz[d + 1];
+      for (int d = 0; d < 6; ++d) {
+        tp.lz[d] = tp.lz[d + 1];
+        if (ENT) tp.sz[d] = tp.sz[d + 1];
+      }
+      tp.lz[6] = nl;
+      if (ENT) tp.sz[6] = ns;
     }
-    tp.lz[6] = nl;
-    if (ENT) tp.sz[6] = ns;
     pdf += sz;
     pfo += sz;
     pnx += sz;
     if (++sc_slot == V5_NSCAL) { sc_slot = 0; sc_par ^= 1; }
     // this warp is done with plane z-2's ring slot and with this scalar slot
     if (z + 1 < zc1 && tid >= 32) named_bar_arrive(1 + (j0 & 3), V2_THREADS);
+  }
+  if (TM) {
+    tmem_wait_st();
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (tid < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(*tm_slot) : "memory");
   }
 }
 
