@@ -564,7 +564,7 @@ template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false> static voi
   rhs_update_v2<ENT, MAG, HYP, UPW, TRAIL><<<g, b, L::SMEM_BYTES, st>>>(tm, S.tmap_df, v);
 }
 
-template <bool ENT, bool MAG, bool HYP, bool UPW, bool TM = false> static void launch_update_v5(const UpdateArgs &a, cudaStream_t st) {
+template <bool ENT, bool MAG, bool HYP, bool UPW, int TM = 0> static void launch_update_v5(const UpdateArgs &a, cudaStream_t st) {
   typedef V5Layout<ENT, MAG> L;
   static bool attr_set = false;
   if (!attr_set) {
@@ -626,7 +626,8 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   }
 #define DISPATCH(E, M, H, U)                                   \
   do {                                                         \
-    if (S.variant == 6) launch_update_v5<E, M, H, U, true>(a, st); \
+    if (S.variant == 7) launch_update_v5<E, M, H, U, 2>(a, st); \
+    else if (S.variant == 6) launch_update_v5<E, M, H, U, 1>(a, st); \
     else if (S.variant == 5) launch_update_v5<E, M, H, U>(a, st);   \
     else if (S.variant == 4) launch_update_v2<E, M, H, U, true>(a, st); \
     else if (S.variant == 3) launch_update_v3<E, M, H, U>(a, st);   \
@@ -1131,7 +1132,7 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   // kernel variant: TMA needs 16-byte global strides -> mx even
   const bool tma_ok = (P.mx % 2 == 0);
   const int kv = S.cfg.kernel_variant;
-  if (kv < 0 || kv > 6) die("kernel_variant=%d unknown (0 = auto, 1 ... 6)", kv);
+  if (kv < 0 || kv > 7) die("kernel_variant=%d unknown (0 = auto, 1 ... 7)", kv);
   if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
   const bool iso = S.cfg.dx == S.cfg.dy && S.cfg.dy == S.cfg.dz; // variant 5 shares one set of stencil weights
   S.variant = kv ? kv : (tma_ok ? (iso ? 5 : 4) : 1);

@@ -34,29 +34,56 @@ template <bool ENT, bool MAG> struct V5Layout {
 };
 
 // ---- tensor memory (TMEM) as per-thread scratch: tcgen05.ld/st, shape 32x32b (lane = thread, 32-bit columns)
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t r[16]) {
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-                 "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-               : "r"(taddr));
-  // the registers are only valid after the wait: passing them through it orders every use behind it
-  asm volatile("tcgen05.wait::ld.sync.aligned;"
-               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]),
-                 "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15])::"memory");
+// The 32-bit halves are packed / unpacked inside the asm block (mov.b64 with register pairs costs nothing once ptxas
+// has allocated aligned pairs), and the wait sits in the same block, so no use can be scheduled before it.
+__device__ __forceinline__ void tmem_ld6d(uint32_t taddr, double h[6]) { // 6 doubles = columns 0..11 (x8 + x4)
+  asm volatile(
+      "{\n\t.reg .b32 t<12>;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {t0, t1, t2, t3, t4, t5, t6, t7}, [%6];\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x4.b32 {t8, t9, t10, t11}, [%7];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 %0, {t0, t1};\n\tmov.b64 %1, {t2, t3};\n\tmov.b64 %2, {t4, t5};\n\t"
+      "mov.b64 %3, {t6, t7};\n\tmov.b64 %4, {t8, t9};\n\tmov.b64 %5, {t10, t11};\n\t}"
+      : "=d"(h[0]), "=d"(h[1]), "=d"(h[2]), "=d"(h[3]), "=d"(h[4]), "=d"(h[5])
+      : "r"(taddr), "r"(taddr + 8)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld7d(uint32_t taddr, double h[7]) { // 7 doubles (+1 spare) = columns 0..15
+  double spare;
+  asm volatile(
+      "{\n\t.reg .b32 t<16>;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {t0, t1, t2, t3, t4, t5, t6, t7, t8, t9, t10, t11, t12, t13, t14, t15}, [%8];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 %0, {t0, t1};\n\tmov.b64 %1, {t2, t3};\n\tmov.b64 %2, {t4, t5};\n\tmov.b64 %3, {t6, t7};\n\t"
+      "mov.b64 %4, {t8, t9};\n\tmov.b64 %5, {t10, t11};\n\tmov.b64 %6, {t12, t13};\n\tmov.b64 %7, {t14, t15};\n\t}"
+      : "=d"(h[0]), "=d"(h[1]), "=d"(h[2]), "=d"(h[3]), "=d"(h[4]), "=d"(h[5]), "=d"(h[6]), "=d"(spare)
+      : "r"(taddr)
+      : "memory");
+  (void)spare;
 }
 __device__ __forceinline__ void tmem_st2d(uint32_t taddr, double a, double b) { // 2 doubles = 4 columns
-  asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(__double2loint(a)),
-               "r"(__double2hiint(a)), "r"(__double2loint(b)), "r"(__double2hiint(b))
-               : "memory");
+  asm volatile(
+      "{\n\t.reg .b32 t<4>;\n\tmov.b64 {t0, t1}, %1;\n\tmov.b64 {t2, t3}, %2;\n\t"
+      "tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {t0, t1, t2, t3};\n\t}" ::"r"(taddr), "d"(a), "d"(b)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st4d(uint32_t taddr, double a, double b, double c, double d) { // 4 doubles = 8 columns
+  asm volatile(
+      "{\n\t.reg .b32 t<8>;\n\tmov.b64 {t0, t1}, %1;\n\tmov.b64 {t2, t3}, %2;\n\tmov.b64 {t4, t5}, %3;\n\tmov.b64 {t6, t7}, %4;\n\t"
+      "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {t0, t1, t2, t3, t4, t5, t6, t7};\n\t}" ::"r"(taddr), "d"(a), "d"(b), "d"(c), "d"(d)
+      : "memory");
 }
 __device__ __forceinline__ void tmem_st1d(uint32_t taddr, double a) { // 1 double = 2 columns
-  asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" ::"r"(taddr), "r"(__double2loint(a)), "r"(__double2hiint(a)) : "memory");
+  asm volatile("{\n\t.reg .b32 t<2>;\n\tmov.b64 {t0, t1}, %1;\n\ttcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {t0, t1};\n\t}" ::"r"(taddr), "d"(a)
+               : "memory");
 }
 __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-// tap policy (interface of SmemLines, pcb200_fast.cuh).  TM: the z histories of lnrho / ss live in TMEM (8 doubles =
-// 16 columns per variable and thread, entries f(z-3..z+3) + 1 spare) instead of two 7-deep register pipelines.
-template <bool ENT, bool MAG, bool TM = false> struct RingLines5 {
+// tap policy (interface of SmemLines, pcb200_fast.cuh).  TM >= 1: the z histories of lnrho / ss live in TMEM (8 doubles
+// = 16 columns per variable and thread, entries f(z-3..z+3) + 1 spare) instead of two 7-deep register pipelines.
+// TM == 2: the own-column z taps f(z-3..z+2) of the six ring fields live there as well (columns 32 + 16 r); only the
+// newest tap f(z+3) is read from the ring: 4 LDS per field and plane less, no z-3 registers.
+template <bool ENT, bool MAG, int TM = 0> struct RingLines5 {
   typedef Slots<ENT> S;
   uint32_t tm; // TMEM address (lane base of the warp, first column) of this thread's lnrho history; ss at +16
   static constexpr bool TRAIL = true, ISO = true;
@@ -131,24 +158,29 @@ template <bool ENT, bool MAG, bool TM = false> struct RingLines5 {
   // (entry 6 = f(z+4) follows at the end of the iteration, when the global load has landed)
   __device__ __forceinline__ void tm_zline(int k, double m[3], double p[3]) {
     const uint32_t a = tm + (k == S::ILN ? 0 : 16);
-    uint32_t r[16];
-    tmem_ld16(a, r);
     double h[7];
-#pragma unroll
-    for (int i = 0; i < 7; ++i) h[i] = __hiloint2double((int)r[2 * i + 1], (int)r[2 * i]);
+    tmem_ld7d(a, h);
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       m[i] = h[2 - i];
       p[i] = h[4 + i];
     }
-    tmem_st2d(a + 0, h[1], h[2]);
-    tmem_st2d(a + 4, h[3], h[4]);
+    tmem_st4d(a + 0, h[1], h[2], h[3], h[4]);
     tmem_st2d(a + 8, h[5], h[6]);
   }
   __device__ __forceinline__ void line(int k, int dir, double m[3], double p[3]) {
     if (is_ring(k)) {
       const int f = foff(k);
-      if (dir == 2) {
+      if (dir == 2 && TM == 2) {
+        const uint32_t a = tm + 32 + 16 * ridx(k);
+        double h[6];
+        tmem_ld6d(a, h);
+        const double fresh = pl[5][f]; // f(z+3)
+        m[0] = h[2]; m[1] = h[1]; m[2] = h[0];
+        p[0] = h[4]; p[1] = h[5]; p[2] = fresh;
+        tmem_st4d(a + 0, h[1], h[2], h[3], h[4]);
+        tmem_st2d(a + 8, h[5], fresh);
+      } else if (dir == 2) {
         m[0] = pl[1][f];
         m[1] = pl[0][f];
         m[2] = zm3[ridx(k)];
@@ -202,7 +234,7 @@ template <bool ENT, bool MAG, bool TM = false> struct RingLines5 {
 
 extern __shared__ __align__(1024) double v5_smem[];
 
-template <bool ENT, bool MAG, bool HYP, bool UPW, bool TM = false>
+template <bool ENT, bool MAG, bool HYP, bool UPW, int TM = 0>
 __global__ void __launch_bounds__(V2_THREADS, 1)
     rhs_update_v5(const __grid_constant__ CUtensorMap tmap_ring, const __grid_constant__ CUtensorMap tmap_scal, const V2Args a) {
   typedef V5Layout<ENT, MAG> L;
@@ -230,9 +262,10 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   uint32_t *tm_slot = reinterpret_cast<uint32_t *>(bar_scal + V5_NSCAL);
-  if (TM) { // 64 TMEM columns: 2 variables x 16 columns per thread, two warps share each lane quarter
+  constexpr int TM_COLS = TM == 2 ? 256 : 64; // 16 columns per variable and thread, two warps share each lane quarter
+  if (TM) {
     if (tid < 32) {
-      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_u32(tm_slot)) : "memory");
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tm_slot)), "n"(TM_COLS) : "memory");
       asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -264,7 +297,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
 
   RingLines5<ENT, MAG, TM> tp;
   tp.trail_zero();
-  if (TM) tp.tm = *tm_slot + ((uint32_t)((tid >> 5) & 3) << 21) + (uint32_t)(tid >> 7) * 32; // lane (warp%4)*32, column (warp/4)*32
+  if (TM) tp.tm = *tm_slot + ((uint32_t)((tid >> 5) & 3) << 21) + (uint32_t)(tid >> 7) * (TM_COLS / 2); // lane (warp%4)*32, column half
   const int toff = (ty + NG) * V2_HX + (tx + NG);
   const long long sv = cP.sv, sz = cP.sz;
   const long long col = ixc + cP.sy * iyc;
@@ -278,7 +311,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
         for (int d = 0; d < 7; ++d) h[d] = __ldg(gl + v * sv + sz * d);
         h[7] = 0.0;
 #pragma unroll
-        for (int d = 0; d < 4; ++d) tmem_st2d(tp.tm + 16 * v + 4 * d, h[2 * d], h[2 * d + 1]);
+        for (int d = 0; d < 2; ++d) tmem_st4d(tp.tm + 16 * v + 8 * d, h[4 * d], h[4 * d + 1], h[4 * d + 2], h[4 * d + 3]);
       }
     } else {
 #pragma unroll
@@ -352,8 +385,19 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
       tp.trail_prologue(0, q3);
       if (MAG) tp.trail_prologue(1, q3);
 #pragma unroll
-      for (int r = 0; r < RingLines5<ENT, MAG>::NR; ++r)
-        tp.zm3[r] = q3[0][r < 3 ? r * V2_PLANE : V5_GROUP + (r - 3) * V2_PLANE];
+      for (int r = 0; r < RingLines5<ENT, MAG>::NR; ++r) {
+        const int fo = r < 3 ? r * V2_PLANE : V5_GROUP + (r - 3) * V2_PLANE;
+        if (TM == 2) { // own-column history f(z-3..z+2) = ring planes 0..5
+          double h[6];
+#pragma unroll
+          for (int d = 0; d < 6; ++d) h[d] = ring[d * L::SLOT + toff + fo];
+#pragma unroll
+          for (int d = 0; d < 3; ++d) tmem_st2d(tp.tm + 32 + 16 * r + 4 * d, h[2 * d], h[2 * d + 1]);
+        } else {
+          tp.zm3[r] = q3[0][fo];
+        }
+      }
+      if (TM == 2) tmem_wait_st();
     }
 
     if (TM) tmem_wait_st(); // the history stores of the previous plane (or of the prologue) are complete
@@ -405,7 +449,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     tmem_wait_st();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (tid < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(*tm_slot) : "memory");
+    if (tid < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(*tm_slot), "n"(TM_COLS) : "memory");
   }
 }
 

@@ -33,7 +33,7 @@ def _cfg(name, **over):
     return c
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7])
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_one_substep(oracle_mod, name, variant):
     """variant 1 = global-load kernel, 2 = TMA/shared-memory z-marching kernel (needs even mx),
@@ -46,7 +46,7 @@ def test_one_substep(oracle_mod, name, variant):
     assert err.max() <= TOL_SUBSTEP, (name, variant, err)
 
 
-@pytest.mark.parametrize("variant", [2, 3, 4, 5, 6])
+@pytest.mark.parametrize("variant", [2, 3, 4, 5, 6, 7])
 @pytest.mark.parametrize("shape", [(32, 8, 4), (64, 16, 40), (70, 9, 5), (6, 6, 6), (34, 10, 17)])
 def test_tma_variants_tile_edges(oracle_mod, shape, variant):
     """grids that are not multiples of the 32x8 tile, shorter than one tile, and z-chunk remainders"""
@@ -213,7 +213,7 @@ def test_p2p_put_path_loopback(oracle_mod, monkeypatch, overlap):
             assert abs(a[k] - b[k]) <= 1e-11 * abs(b[k])
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7])
 @pytest.mark.parametrize("overlap", [True, False])
 def test_exchange_code_path_loopback(oracle_mod, monkeypatch, variant, overlap):
     """The multi-GPU code path on ONE GPU: PCB200_LOOPBACK=1 makes every neighbour this rank, so the y-face
