@@ -81,11 +81,16 @@ __device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.
 
 // tap policy (interface of SmemLines, pcb200_fast.cuh).  TM >= 1: the z histories of lnrho / ss live in TMEM (8 doubles
 // = 16 columns per variable and thread, entries f(z-3..z+3) + 1 spare) instead of two 7-deep register pipelines.
-// TM == 2: the own-column z taps f(z-3..z+2) of the six ring fields live there as well (columns 32 + 16 r); only the
-// newest tap f(z+3) is read from the ring: 4 LDS per field and plane less, no z-3 registers.
+// TM == 2: the own-column z taps f(z-3..z+2) of the six ring fields live there as well; only the newest tap f(z+3) is
+// read from the ring: 4 LDS per field and plane less, no z-3 registers.  All eight histories are circular (32 columns
+// per variable and thread = the whole 512-column TMEM for the two warps of a lane quarter).
 template <bool ENT, bool MAG, int TM = 0> struct RingLines5 {
   typedef Slots<ENT> S;
   uint32_t tm; // TMEM address (lane base of the warp, first column) of this thread's lnrho history; ss at +16
+  // TM == 2: circular histories, 8 entries per variable stored twice (entry e at 2e and 2e+16 of the variable's 32
+  // columns) so that every window of consecutive planes is contiguous and nothing is ever shifted:
+  uint32_t tw;    // column offset of the window start (plane z-3) in this iteration: 2*(j0 mod 8)
+  uint32_t tnew;  // column offset of the entry that receives this iteration's new plane
   static constexpr bool TRAIL = true, ISO = true;
   static constexpr int NR = MAG ? 6 : 3;
   static __device__ __forceinline__ int dr(int) { return 0; }
@@ -157,8 +162,17 @@ template <bool ENT, bool MAG, int TM = 0> struct RingLines5 {
   // TMEM history of a scalar: taps of this plane, and the history shifted by one plane written back
   // (entry 6 = f(z+4) follows at the end of the iteration, when the global load has landed)
   __device__ __forceinline__ void tm_zline(int k, double m[3], double p[3]) {
-    const uint32_t a = tm + (k == S::ILN ? 0 : 16);
     double h[7];
+    if (TM == 2) { // circular: nothing to write back
+      tmem_ld7d(tm + (k == S::ILN ? 0 : 32) + tw, h);
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        m[i] = h[2 - i];
+        p[i] = h[4 + i];
+      }
+      return;
+    }
+    const uint32_t a = tm + (k == S::ILN ? 0 : 16);
     tmem_ld7d(a, h);
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
@@ -172,14 +186,14 @@ template <bool ENT, bool MAG, int TM = 0> struct RingLines5 {
     if (is_ring(k)) {
       const int f = foff(k);
       if (dir == 2 && TM == 2) {
-        const uint32_t a = tm + 32 + 16 * ridx(k);
+        const uint32_t a = tm + 64 + 32 * ridx(k);
         double h[6];
-        tmem_ld6d(a, h);
-        const double fresh = pl[5][f]; // f(z+3)
+        tmem_ld6d(a + tw, h);          // f(z-3..z+2)
+        const double fresh = pl[5][f]; // f(z+3): the new entry of the circular history (both copies)
         m[0] = h[2]; m[1] = h[1]; m[2] = h[0];
         p[0] = h[4]; p[1] = h[5]; p[2] = fresh;
-        tmem_st4d(a + 0, h[1], h[2], h[3], h[4]);
-        tmem_st2d(a + 8, h[5], fresh);
+        tmem_st1d(a + tnew, fresh);
+        tmem_st1d(a + tnew + 16, fresh);
       } else if (dir == 2) {
         m[0] = pl[1][f];
         m[1] = pl[0][f];
@@ -262,7 +276,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   uint32_t *tm_slot = reinterpret_cast<uint32_t *>(bar_scal + V5_NSCAL);
-  constexpr int TM_COLS = TM == 2 ? 256 : 64; // 16 columns per variable and thread, two warps share each lane quarter
+  constexpr int TM_COLS = TM == 2 ? 512 : 64; // 16 (TM=1) or 32 (TM=2) columns per variable and thread, two warps share each lane quarter
   if (TM) {
     if (tid < 32) {
       asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tm_slot)), "n"(TM_COLS) : "memory");
@@ -311,7 +325,14 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
         for (int d = 0; d < 7; ++d) h[d] = __ldg(gl + v * sv + sz * d);
         h[7] = 0.0;
 #pragma unroll
-        for (int d = 0; d < 2; ++d) tmem_st4d(tp.tm + 16 * v + 8 * d, h[4 * d], h[4 * d + 1], h[4 * d + 2], h[4 * d + 3]);
+        for (int d = 0; d < 2; ++d) {
+          if (TM == 2) { // planes 0..6 at entries 0..6, both copies
+            tmem_st4d(tp.tm + 32 * v + 8 * d, h[4 * d], h[4 * d + 1], h[4 * d + 2], h[4 * d + 3]);
+            tmem_st4d(tp.tm + 32 * v + 16 + 8 * d, h[4 * d], h[4 * d + 1], h[4 * d + 2], h[4 * d + 3]);
+          } else {
+            tmem_st4d(tp.tm + 16 * v + 8 * d, h[4 * d], h[4 * d + 1], h[4 * d + 2], h[4 * d + 3]);
+          }
+        }
       }
     } else {
 #pragma unroll
@@ -387,12 +408,15 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
 #pragma unroll
       for (int r = 0; r < RingLines5<ENT, MAG>::NR; ++r) {
         const int fo = r < 3 ? r * V2_PLANE : V5_GROUP + (r - 3) * V2_PLANE;
-        if (TM == 2) { // own-column history f(z-3..z+2) = ring planes 0..5
+        if (TM == 2) { // own-column history f(z-3..z+2) = ring planes 0..5 at entries 0..5, both copies
           double h[6];
 #pragma unroll
           for (int d = 0; d < 6; ++d) h[d] = ring[d * L::SLOT + toff + fo];
 #pragma unroll
-          for (int d = 0; d < 3; ++d) tmem_st2d(tp.tm + 32 + 16 * r + 4 * d, h[2 * d], h[2 * d + 1]);
+          for (int d = 0; d < 3; ++d) {
+            tmem_st2d(tp.tm + 64 + 32 * r + 4 * d, h[2 * d], h[2 * d + 1]);
+            tmem_st2d(tp.tm + 64 + 32 * r + 16 + 4 * d, h[2 * d], h[2 * d + 1]);
+          }
         } else {
           tp.zm3[r] = q3[0][fo];
         }
@@ -401,6 +425,10 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
     }
 
     if (TM) tmem_wait_st(); // the history stores of the previous plane (or of the prologue) are complete
+    if (TM == 2) {
+      tp.tw = 2u * (uint32_t)(j0 & 7);
+      tp.tnew = 2u * (uint32_t)((j0 + 6) & 7); // ring fields: plane z+3
+    }
     double rhs[NV], fc[NV];
     // TM: every thread evaluates the cell (tcgen05.ld/st are warp-collective; threads outside the grid work on
     // zero-filled TMA data and store nothing)
@@ -426,7 +454,15 @@ __global__ void __launch_bounds__(V2_THREADS, 1)
       }
     }
     // advance the scalar pipelines and the running pointers
-    if (TM) {
+    if (TM == 2) { // scalars: plane z+4 = entry (j0+7) mod 8, both copies
+      const uint32_t e = 2u * (uint32_t)((j0 + 7) & 7);
+      tmem_st1d(tp.tm + e, nl);
+      tmem_st1d(tp.tm + e + 16, nl);
+      if (ENT) {
+        tmem_st1d(tp.tm + 32 + e, ns);
+        tmem_st1d(tp.tm + 32 + e + 16, ns);
+      }
+    } else if (TM) {
       tmem_st1d(tp.tm + 12, nl);
       if (ENT) tmem_st1d(tp.tm + 16 + 12, ns);
     } else {
