@@ -115,6 +115,10 @@ void pcb200_p2p_export(unsigned char *blob);
 int pcb200_p2p_connect(const unsigned char *blobs, const int *nranks);
 /* call on all ranks after every rank's connect returned 0 (the host reduces the status: MPI_ALLREDUCE / all_reduce) */
 void pcb200_p2p_enable(void);
+/* asynchronous copy_farray (extension): device-side snapshot in stream order, device-to-host transfer on a
+   copy stream overlapping the following substeps; _wait blocks until the host array f is complete */
+void pcb200_copy_farray_async(double *f);
+void pcb200_copy_farray_wait(void);
 /* block until all queued device work has finished */
 void pcb200_synchronize(void);
 /* device-side synthetic initial condition written straight into the device f-array */

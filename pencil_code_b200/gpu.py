@@ -62,6 +62,7 @@ ABI_SYMBOLS = (
     "pcb200_set_stream", "pcb200_synchronize", "pcb200_init_synthetic", "pcb200_launch_count",
     "pcb200_kernel_timing", "pcb200_enable_kernel_timing",
     "pcb200_p2p_blob_bytes", "pcb200_p2p_export", "pcb200_p2p_connect", "pcb200_p2p_enable",
+    "pcb200_copy_farray_async", "pcb200_copy_farray_wait",
     "initialize_gpu_c", "register_gpu_c", "finalize_gpu_c", "rhs_gpu_c", "before_boundary_gpu_c",
     "update_after_substep_gpu_c", "load_farray_c", "copy_farray_c", "gpu_prepare_for_first_substep_c",
     "get_farray_ptr_gpu_c", "reload_gpu_config_c", "update_on_gpu_scal_by_name_c", "update_on_gpu_vec_by_name_c",
@@ -107,6 +108,7 @@ def load_library():
     L.rhs_gpu_c.argtypes = [ip, dp]
     L.before_boundary_gpu_c.argtypes = [ip, ip, dp, ip]
     L.copy_farray_c.argtypes = [dp]
+    L.pcb200_copy_farray_async.argtypes = [dp]
     L.gpu_prepare_for_first_substep_c.argtypes = [dp]
     L.get_farray_ptr_gpu_c.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
     L.get_gpu_reduced_vars_c.argtypes = [dp]
@@ -171,6 +173,13 @@ class GPU:
         self.L.initialize_gpu_c(_dp(f), C.byref(comm), C.byref(ct), C.byref(cnt), C.byref(z), C.byref(z), C.byref(z))
         if nt > 0:
             self.load_farray_to_GPU(f)
+
+    def copy_farray_from_GPU_async(self, f):
+        """start a snapshot + asynchronous device-to-host copy of the current f; pair with copy_farray_wait()"""
+        self.L.pcb200_copy_farray_async(_dp(f))
+
+    def copy_farray_wait(self):
+        self.L.pcb200_copy_farray_wait()
 
     # --- z-halo over NVLink peer memory (include/pcb200.h: pcb200_p2p_*) ---------
     def p2p_export(self):

@@ -180,6 +180,30 @@ def test_full_size_512_independent_kernels_agree_and_ghosts_wrap():
     assert np.array_equal(a[:, :3], a[:, n:n + 3]) and np.array_equal(a[:, n + 3:], a[:, 3:6])
 
 
+def test_async_copy_is_a_snapshot():
+    """pcb200_copy_farray_async: the host array receives the state at the time of the call even though the time loop
+    keeps running while the transfer is in flight"""
+    from pencil_code_b200.gpu import GPU
+    cfg = pcfg.make_config(64, True, True, nu=5e-3, eta=5e-3, chi=5e-3)
+    f = synthetic.initial_condition(cfg)
+    g = GPU(cfg)
+    g.initialize_GPU(f)
+    dt, t = pcfg.fixed_dt(cfg), 0.0
+    _, t = g.time_step(f, dt, False, t)
+    ref = np.empty_like(f)
+    g.copy_farray_from_GPU(ref)            # synchronous copy of the state after step 1
+    snap = np.zeros_like(f)
+    g.copy_farray_from_GPU_async(snap)     # asynchronous snapshot of the same state ...
+    for _ in range(3):                     # ... while three more steps run
+        _, t = g.time_step(f, dt, False, t)
+    g.copy_farray_wait()
+    later = np.empty_like(f)
+    g.copy_farray_from_GPU(later)
+    g.finalize_GPU()
+    assert np.array_equal(snap, ref)
+    assert not np.array_equal(later, ref)
+
+
 def test_zero_velocity_uniform_state_is_steady(oracle_mod):
     """edge case: uniform state has zero RHS (up to FMA-contraction rounding of the der2 weights)"""
     from pencil_code_b200.gpu import GPU
