@@ -477,6 +477,7 @@ static void derive_pars() {
     for (int i = 0; i < 3; ++i) { P.d1c[j][i] = P.d1fac[j] * w1[i]; P.dmc[j][i] = P.dmfac[j] * wm[i]; }
     for (int i = 0; i < 4; ++i) P.d2c[j][i] = P.d2fac[j] * w2[i];
   }
+  P.d2c0x2 = 2.0 * P.d2c[0][0]; P.d2c0x3 = 3.0 * P.d2c[0][0];
   P.dxyz_2 = d1[0] * d1[0] + d1[1] * d1[1] + d1[2] * d1[2];
   P.dxyz_4 = std::pow(d1[0], 4) + std::pow(d1[1], 4) + std::pow(d1[2], 4);
   P.dxyz_6 = std::pow(d1[0], 6) + std::pow(d1[1], 6) + std::pow(d1[2], 6);

@@ -35,6 +35,7 @@ struct Pars {
   double d1c[3][3];     // d1fac * (45, -9, 1)
   double d2c[3][4];     // d2fac * (-490, 270, -27, 2)/180
   double dmc[3][3];     // dmfac * (270, -27, 2)
+  double d2c0x2, d2c0x3; // 2x / 3x the centre weight of der2 (isotropic grids: second derivatives summed over directions)
   double dline_1[3];
   double dxyz_2, dxyz_4, dxyz_6;
   double cs20, gamma, gamma1, gamma_m1, cp, cp1, cv1, lnrho0, lnTT0, TT0_1; // TT0_1 = exp(-lnTT0)

@@ -43,9 +43,25 @@ __device__ __forceinline__ double exp_fast(double x) {
   return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
 }
 
+// Isotropic grids (one set of der2 weights): the symmetric tap sums p_k + m_k of several directions are added up
+// first and weighted once -- sum_j der2_j(f) = n c0 f + c1 S0 + c2 S1 + c3 S2 with S_k = sum_j (p_jk + m_jk) --
+// which saves 4 FP64 operations per Laplacian and 2-3 per (diagonal + rest) pair.
+struct SymSum {
+  double s0, s1, s2;
+  bool first = true;
+  __device__ __forceinline__ void add(const double m[3], const double p[3]) {
+    if (first) { s0 = p[0] + m[0]; s1 = p[1] + m[1]; s2 = p[2] + m[2]; first = false; }
+    else { s0 += p[0] + m[0]; s1 += p[1] + m[1]; s2 += p[2] + m[2]; }
+  }
+  // c0n = n * d2c[0][0] for the n directions that were added
+  __device__ __forceinline__ double weighted(double c, double c0n) const {
+    return (c0n * c + cP.d2c[0][1] * s0) + (cP.d2c[0][2] * s1 + cP.d2c[0][3] * s2);
+  }
+};
+
 // Policy adapter: global memory lines (lets variant-2 physics run on the variant-1 access path)
 struct GlobalLines {
-  static constexpr bool TRAIL = false;
+  static constexpr bool TRAIL = false, ISO = false;
   static __device__ __forceinline__ int dr(int j) { return j; } // index of the per-direction stencil weights
   static __device__ __forceinline__ int pr(int p) { return p; } // index of the per-pair mixed-derivative weights
   const double *__restrict__ c0;
@@ -95,12 +111,14 @@ __device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, doub
   fc[S::ILN] = lnrho;
   ho.lnrho = lnrho;
   double gl[3], del2lnrho = 0.0, del6lnrho = 0.0, upw_l = 0.0;
+  SymSum sl;
 #pragma unroll
   for (int j = 0; j < 3; ++j) {
     double m[3], p[3];
     tp.line(S::ILN, j, m, p);
     gl[j] = d1_line(m, p, T::dr(j));
-    if (ENT) del2lnrho += d2_line(lnrho, m, p, T::dr(j));
+    if (ENT && T::ISO) sl.add(m, p);
+    else if (ENT) del2lnrho += d2_line(lnrho, m, p, T::dr(j));
     if (HYP || UPW) {
       const double r6 = d6raw_line(lnrho, m, p);
       if (HYP) del6lnrho += P.d6fac[T::dr(j)] * r6;
@@ -108,11 +126,14 @@ __device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, doub
     }
   }
 
+  if (ENT && T::ISO) del2lnrho = sl.weighted(lnrho, P.d2c0x3);
+
   // ---- velocity: gradient tensor, laplacian, diagonal second derivatives
   double uij[3][3], del2u[3], graddivu[3], hyp[3] = {0., 0., 0.}, upw_u[3] = {0., 0., 0.};
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
     double d2s = 0.0;
+    SymSum su;
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
       double m[3], p[3];
@@ -124,9 +145,13 @@ __device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, doub
         if (i == 0 && j == 0) tp.trail_add(0, 2, 2, m, p);
         if (i == 1 && j == 1) tp.trail_add(0, 2, 1, m, p);
       }
-      const double d2 = d2_line(u[i], m, p, T::dr(j));
-      d2s += d2;
-      if (j == i) graddivu[i] = d2; // fjji(i,i)=der2 (sub.f90:2651-2653)
+      if (T::ISO && j != i) {
+        su.add(m, p); // the two off-diagonal second derivatives only enter through their sum
+      } else {
+        const double d2 = d2_line(u[i], m, p, T::dr(j));
+        d2s += d2;
+        if (j == i) graddivu[i] = d2; // fjji(i,i)=der2 (sub.f90:2651-2653)
+      }
       if (HYP || UPW) {
         const double r6 = d6raw_line(u[i], m, p);
         if (HYP) {
@@ -136,6 +161,7 @@ __device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, doub
         if (UPW) upw_u[i] += au[j] * (P.d6upfac[T::dr(j)] * r6);
       }
     }
+    if (T::ISO) d2s += su.weighted(u[i], P.d2c0x2);
     del2u[i] = d2s;
   }
   // mixed derivatives for grad div u: fjji(i,j)=d_i d_j u_j
@@ -202,14 +228,17 @@ __device__ __forceinline__ void hydro_part(T &tp, double *__restrict__ rhs, doub
     const double ss = tp.c(S::ISS);
     fc[S::ISS] = ss;
     double gss[3], del2ss = 0.0, upw_s = 0.0;
+    SymSum sss;
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
       double m[3], p[3];
       tp.line(S::ISS, j, m, p);
       gss[j] = d1_line(m, p, T::dr(j));
-      del2ss += d2_line(ss, m, p, T::dr(j));
+      if (T::ISO) sss.add(m, p);
+      else del2ss += d2_line(ss, m, p, T::dr(j));
       if (UPW) upw_s += au[j] * (P.d6upfac[T::dr(j)] * d6raw_line(ss, m, p));
     }
+    if (T::ISO) del2ss = sss.weighted(ss, P.d2c0x3);
     const double e = P.cv1 * ss + P.gamma_m1 * (lnrho - P.lnrho0);
     const double ex = exp_fast(e);
     const double cs2 = P.cs20 * ex;
@@ -250,11 +279,13 @@ __device__ __forceinline__ void mag_part(T &tp, const double u[3], double *__res
   if (T::TRAIL) tp.trail_pop(1, tg);
   const bool upa = UPW && P.lupw_aa;
   const double au[3] = {fabs(u[0]), fabs(u[1]), fabs(u[2])};
-  double aij[3][3], dd[3][3], upw_a[3] = {0., 0., 0.};
+  constexpr bool SUM = T::ISO && T::TRAIL; // diagonal second derivative + summed rest (see SymSum)
+  double aij[3][3], dd[3][3], dia[3], rest[3], upw_a[3] = {0., 0., 0.};
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
     const double a = tp.c(S::IAX + i);
     fc[S::IAX + i] = a;
+    SymSum sa;
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
       double m[3], p[3];
@@ -266,17 +297,29 @@ __device__ __forceinline__ void mag_part(T &tp, const double u[3], double *__res
         if (i == 1 && j == 1) tp.trail_add(1, 2, 1, m, p);
       }
       aij[i][j] = (i != j || upa) ? d1_line(m, p, T::dr(j)) : 0.0;
-      dd[i][j] = d2_line(a, m, p, T::dr(j));
+      if (SUM) {
+        if (j == i) dia[i] = d2_line(a, m, p, T::dr(j));
+        else sa.add(m, p);
+      } else {
+        dd[i][j] = d2_line(a, m, p, T::dr(j));
+      }
       if (UPW && j != i) upw_a[i] += au[j] * (P.d6upfac[T::dr(j)] * d6raw_line(a, m, p)); // mask=i (magnetic.f90:6301)
     }
+    if (SUM) rest[i] = sa.weighted(a, P.d2c0x2);
   }
   const double bb[3] = {aij[2][1] - aij[1][2], aij[0][2] - aij[2][0], aij[1][0] - aij[0][1]};
   double jj[3];
   if (T::TRAIL) { // jj = mu01*(grad div A - del2 A); z-mixed parts = leading (ring) + trailing (accumulators) halves
     tp.lead(1, tg);
-    jj[0] = P.mu01 * ((tp.dij(S::IAX + 1, 0) + tg[0]) - (dd[0][1] + dd[0][2]));
-    jj[1] = P.mu01 * ((tp.dij(S::IAX + 0, 0) + tg[1]) - (dd[1][2] + dd[1][0]));
-    jj[2] = P.mu01 * (tg[2] - (dd[2][0] + dd[2][1]));
+    if (SUM) {
+      jj[0] = P.mu01 * ((tp.dij(S::IAX + 1, 0) + tg[0]) - rest[0]);
+      jj[1] = P.mu01 * ((tp.dij(S::IAX + 0, 0) + tg[1]) - rest[1]);
+      jj[2] = P.mu01 * (tg[2] - rest[2]);
+    } else {
+      jj[0] = P.mu01 * ((tp.dij(S::IAX + 1, 0) + tg[0]) - (dd[0][1] + dd[0][2]));
+      jj[1] = P.mu01 * ((tp.dij(S::IAX + 0, 0) + tg[1]) - (dd[1][2] + dd[1][0]));
+      jj[2] = P.mu01 * (tg[2] - (dd[2][0] + dd[2][1]));
+    }
   } else {
     const double a1_xy = tp.dij(S::IAX + 0, 0), a1_zx = tp.dij(S::IAX + 0, 2);
     const double a2_xy = tp.dij(S::IAX + 1, 0), a2_yz = tp.dij(S::IAX + 1, 1);
@@ -292,7 +335,7 @@ __device__ __forceinline__ void mag_part(T &tp, const double u[3], double *__res
   double fres[3] = {0., 0., 0.};
   if (P.lresi_eta_const) {
 #pragma unroll
-    for (int i = 0; i < 3; ++i) fres[i] = P.eta * (dd[i][0] + dd[i][1] + dd[i][2]);
+    for (int i = 0; i < 3; ++i) fres[i] = SUM ? P.eta * (dia[i] + rest[i]) : P.eta * (dd[i][0] + dd[i][1] + dd[i][2]);
   }
   if (!upa) {
     rhs[S::IAX + 0] = (u[1] * bb[2] - u[2] * bb[1]) + fres[0];
