@@ -36,8 +36,9 @@ def _cfg(name, **over):
 @pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7])
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_one_substep(oracle_mod, name, variant):
-    """variant 1 = global-load kernel, 2 = TMA/shared-memory z-marching kernel (needs even mx),
-    3 = variant 2 with the physics split over hydro/magnetic warp roles"""
+    """variant 1 = global-load kernel, 2 = TMA/shared-memory z-marching kernel (needs even mx), 3 = 2 with the physics
+    split over hydro/magnetic warp roles, 4 = lead/trail z-mixed derivatives, 5 = isotropic-spacing specialisation
+    (default), 6/7 = 5 with z histories in tensor memory"""
     cfg = _cfg(name)
     if variant >= 2 and cfg["nx"] % 2:
         pytest.skip("TMA variant needs 16-byte row strides (even mx); odd grids use variant 1")
