@@ -7,6 +7,7 @@
 #include "pcb200_fast.cuh"
 #include "pcb200_v3.cuh"
 #include "pcb200_v5.cuh"
+#include "pcb200_v8.cuh"
 #include <cudaTypedefs.h>
 #include "../../include/pcb200.h"
 
@@ -392,6 +393,7 @@ struct State {
   CUtensorMap tmap[2];      // TMA descriptors of f[0], f[1] (kernel variant 2)
   CUtensorMap tmap_df;      // df tiles (32 x 8 x 1 x nvar) for L2 prefetch
   CUtensorMap tmap3_ring[2], tmap3_scal[2]; // variant 3: 3-variable and {lnrho,ss} boxes
+  CUtensorMap tmap8_ring[2], tmap8_scal[2]; // variant 8: the same with (38 x 18) boxes
   int variant = 1;          // kernel actually used (1 = global-load, 2 = smem ring + TMA, 3 = 2 + role split)
   int nsm = 148;
   cudaStream_t stream = nullptr, comm_stream = nullptr;
@@ -592,6 +594,37 @@ template <bool ENT, bool MAG, bool HYP, bool UPW, int TM = 0> static void launch
   rhs_update_v5<ENT, MAG, HYP, UPW, TM><<<g, b, L::SMEM_BYTES, st>>>(S.tmap3_ring[w], S.tmap3_scal[w], v);
 }
 
+template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v8(const UpdateArgs &a, cudaStream_t st) {
+  typedef V8Layout<ENT, MAG> L;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(rhs_update_v8<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    attr_set = true;
+  }
+  V2Args v;
+  v.fin = a.fin; v.fout = a.fout; v.df = a.df; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
+  v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
+  v.df_prefetch = S.df_prefetch;
+  const int gx = (S.P.nx + V8_TX - 1) / V8_TX, gy = (S.P.ny + V8_TY - 1) / V8_TY;
+  const int nzr = a.z_hi - a.z_lo;
+  int nch = (4 * S.nsm + gx * gy - 1) / (gx * gy);
+  { // one CTA per SM: among nch..nch+3 z chunks take the count whose last wave is fullest
+    double best = 0.0;
+    int pick = nch;
+    for (int c = nch; c < nch + 4; ++c) {
+      const double waves = (double)gx * gy * c / S.nsm, eff = waves / std::ceil(waves);
+      if (eff > best + 0.02) { best = eff; pick = c; }
+    }
+    nch = pick;
+  }
+  nch = std::max(1, std::min(nch, std::max(1, nzr / 16)));
+  v.lz = (nzr + nch - 1) / nch;
+  nch = (nzr + v.lz - 1) / v.lz;
+  dim3 g(gx, gy, nch), b(V8_TX, V8_TY, 1);
+  const int w = (a.fin == S.f[0]) ? 0 : 1;
+  rhs_update_v8<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(S.tmap8_ring[w], S.tmap8_scal[w], v);
+}
+
 template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v3(const UpdateArgs &a, cudaStream_t st) {
   typedef V3Layout<ENT, MAG> L;
   static bool attr_set = false;
@@ -632,7 +665,8 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   }
 #define DISPATCH(E, M, H, U)                                   \
   do {                                                         \
-    if (S.variant == 7) launch_update_v5<E, M, H, U, 2>(a, st); \
+    if (S.variant == 8) launch_update_v8<E, M, H, U>(a, st); \
+    else if (S.variant == 7) launch_update_v5<E, M, H, U, 2>(a, st); \
     else if (S.variant == 6) launch_update_v5<E, M, H, U, 1>(a, st); \
     else if (S.variant == 5) launch_update_v5<E, M, H, U>(a, st);   \
     else if (S.variant == 4) launch_update_v2<E, M, H, U, true>(a, st); \
@@ -1146,7 +1180,7 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   // kernel variant: TMA needs 16-byte global strides -> mx even
   const bool tma_ok = (P.mx % 2 == 0);
   const int kv = S.cfg.kernel_variant;
-  if (kv < 0 || kv > 7) die("kernel_variant=%d unknown (0 = auto, 1 ... 7)", kv);
+  if (kv < 0 || kv > 8) die("kernel_variant=%d unknown (0 = auto, 1 ... 8)", kv);
   if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
   const bool iso = S.cfg.dx == S.cfg.dy && S.cfg.dy == S.cfg.dz; // variant 5 shares one set of stencil weights
   S.variant = kv ? kv : (tma_ok ? (iso ? 5 : 4) : 1);
@@ -1160,6 +1194,12 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
     for (int w = 0; w < 2; ++w) {
       make_tensor_map(&S.tmap3_ring[w], S.f[w], V3_HX, V3_HY, 3);
       make_tensor_map(&S.tmap3_scal[w], S.f[w], V3_HX, V3_HY, S.cfg.iss >= 0 ? 2 : 1);
+    }
+  }
+  if (S.variant == 8) {
+    for (int w = 0; w < 2; ++w) {
+      make_tensor_map(&S.tmap8_ring[w], S.f[w], V8_HX, V8_HY, 3);
+      make_tensor_map(&S.tmap8_scal[w], S.f[w], V8_HX, V8_HY, S.cfg.iss >= 0 ? 2 : 1);
     }
   }
   // halo machinery: yz-pencils need y-face staging; z exchange is overlapped with the interior kernel

@@ -33,12 +33,12 @@ def _cfg(name, **over):
     return c
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8])
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_one_substep(oracle_mod, name, variant):
     """variant 1 = global-load kernel, 2 = TMA/shared-memory z-marching kernel (needs even mx), 3 = 2 with the physics
     split over hydro/magnetic warp roles, 4 = lead/trail z-mixed derivatives, 5 = isotropic-spacing specialisation
-    (default), 6/7 = 5 with z histories in tensor memory"""
+    (default), 6/7 = 5 with z histories in tensor memory, 8 = 7 with 12 warps on a 32x12 tile"""
     cfg = _cfg(name)
     if variant >= 2 and cfg["nx"] % 2:
         pytest.skip("TMA variant needs 16-byte row strides (even mx); odd grids use variant 1")
@@ -47,10 +47,10 @@ def test_one_substep(oracle_mod, name, variant):
     assert err.max() <= TOL_SUBSTEP, (name, variant, err)
 
 
-@pytest.mark.parametrize("variant", [2, 3, 4, 5, 6, 7])
+@pytest.mark.parametrize("variant", [2, 3, 4, 5, 6, 7, 8])
 @pytest.mark.parametrize("shape", [(32, 8, 4), (64, 16, 40), (70, 9, 5), (6, 6, 6), (34, 10, 17)])
 def test_tma_variants_tile_edges(oracle_mod, shape, variant):
-    """grids that are not multiples of the 32x8 tile, shorter than one tile, and z-chunk remainders"""
+    """grids that are not multiples of the 32x8 (variant 8: 32x12) tile, shorter than one tile, and z-chunk remainders"""
     nx, ny, nz = shape
     cfg = pcfg.make_config(nx, True, True, ny=ny, nz=nz, nu=5e-3, eta=4e-3, chi=3e-3, cdt=0.4, cdtv=0.3)
     cfg.update(dx=0.2, dy=0.21, dz=0.19)
@@ -238,7 +238,7 @@ def test_p2p_put_path_loopback(oracle_mod, monkeypatch, overlap):
             assert abs(a[k] - b[k]) <= 1e-11 * abs(b[k])
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7])
+@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8])
 @pytest.mark.parametrize("overlap", [True, False])
 def test_exchange_code_path_loopback(oracle_mod, monkeypatch, variant, overlap):
     """The multi-GPU code path on ONE GPU: PCB200_LOOPBACK=1 makes every neighbour this rank, so the y-face
