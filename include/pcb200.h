@@ -65,7 +65,7 @@ typedef struct pcb200_config {
   /* kernel selection: 0 = auto (fastest validated: 5 on isotropic grids, 4 otherwise, 1 when mx is odd),
      1 = global-load kernel, 2 = TMA/shared-memory z-marching kernel, 3 = 2 with the physics split over two warp
      roles, 4 = 2 with lead/trail z-mixed derivatives, 5 = 4 specialised for dx=dy=dz, 6 / 7 = 5 with
-     the z histories of the scalars / of all variables in tensor memory */
+     the z histories of the scalars / of all variables in tensor memory, 8 = 7 with 12 warps on a (32 x 12) tile */
   int kernel_variant;
 } pcb200_config;
 
