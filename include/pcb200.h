@@ -121,6 +121,16 @@ void pcb200_p2p_enable(void);
    copy stream overlapping the following substeps; _wait blocks until the host array f is complete */
 void pcb200_copy_farray_async(double *f);
 void pcb200_copy_farray_wait(void);
+/* var.dat snapshot of this rank in the reference's distributed-I/O layout (src/io_dist.f90:108-199
+   output_snap, :697-788 read_snap): two gfortran sequential unformatted records, {f(mx,my,mz,nvar)} and
+   {t, x(mx), y(my), z(mz), dx, dy, dz}, records above 2 GiB as subrecords.  Host-only (no device work): f is the host
+   f-array, e.g. after pcb200_copy_farray_wait.  By value, not Fortran bindings (the Fortran build keeps its own Io
+   module).  Unlike the device entry points these RETURN a status: 0 ok, 1 I/O error (errno set), 2 file does not have
+   the expected record structure/sizes, 3 bad argument.  dxyz receives dx, dy, dz. */
+int pcb200_write_snapshot(const char *path, const double *f, int mx, int my, int mz, int nvar, double t, const double *x,
+                          const double *y, const double *z, double dx, double dy, double dz);
+int pcb200_read_snapshot(const char *path, double *f, int mx, int my, int mz, int nvar, double *t, double *x, double *y,
+                         double *z, double *dxyz);
 /* block until all queued device work has finished */
 void pcb200_synchronize(void);
 /* device-side synthetic initial condition written straight into the device f-array */

@@ -62,7 +62,7 @@ ABI_SYMBOLS = (
     "pcb200_set_stream", "pcb200_synchronize", "pcb200_init_synthetic", "pcb200_launch_count",
     "pcb200_kernel_timing", "pcb200_enable_kernel_timing",
     "pcb200_p2p_blob_bytes", "pcb200_p2p_export", "pcb200_p2p_connect", "pcb200_p2p_enable",
-    "pcb200_copy_farray_async", "pcb200_copy_farray_wait",
+    "pcb200_copy_farray_async", "pcb200_copy_farray_wait", "pcb200_write_snapshot", "pcb200_read_snapshot",
     "initialize_gpu_c", "register_gpu_c", "finalize_gpu_c", "rhs_gpu_c", "before_boundary_gpu_c",
     "update_after_substep_gpu_c", "load_farray_c", "copy_farray_c", "gpu_prepare_for_first_substep_c",
     "get_farray_ptr_gpu_c", "reload_gpu_config_c", "update_on_gpu_scal_by_name_c", "update_on_gpu_vec_by_name_c",
@@ -100,6 +100,11 @@ def load_library():
     L.pcb200_p2p_export.argtypes = [C.c_char_p]
     L.pcb200_p2p_connect.argtypes = [C.c_char_p, ip]
     L.pcb200_p2p_connect.restype = C.c_int
+    L.pcb200_write_snapshot.argtypes = [C.c_char_p, dp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, dp, dp, dp,
+                                        C.c_double, C.c_double, C.c_double]
+    L.pcb200_write_snapshot.restype = C.c_int
+    L.pcb200_read_snapshot.argtypes = [C.c_char_p, dp, C.c_int, C.c_int, C.c_int, C.c_int, dp, dp, dp, dp, dp]
+    L.pcb200_read_snapshot.restype = C.c_int
     L.pcb200_init_synthetic.argtypes = [ip]
     L.pcb200_launch_count.restype = C.c_longlong
     L.pcb200_kernel_timing.argtypes = [dp, C.POINTER(C.c_longlong), ip]

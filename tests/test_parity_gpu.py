@@ -181,9 +181,10 @@ def test_full_size_512_independent_kernels_agree_and_ghosts_wrap():
     assert np.array_equal(a[:, :3], a[:, n:n + 3]) and np.array_equal(a[:, n + 3:], a[:, 3:6])
 
 
-def test_async_copy_is_a_snapshot():
+def test_async_copy_is_a_snapshot(tmp_path):
     """pcb200_copy_farray_async: the host array receives the state at the time of the call even though the time loop
-    keeps running while the transfer is in flight"""
+    keeps running while the transfer is in flight; written as var.dat it restarts a run bit-identically"""
+    from pencil_code_b200 import snapshot
     from pencil_code_b200.gpu import GPU
     cfg = pcfg.make_config(64, True, True, nu=5e-3, eta=5e-3, chi=5e-3)
     f = synthetic.initial_condition(cfg)
@@ -203,6 +204,19 @@ def test_async_copy_is_a_snapshot():
     g.finalize_GPU()
     assert np.array_equal(snap, ref)
     assert not np.array_equal(later, ref)
+    # restart from the snapshot file (rsnap -> load_farray_to_GPU): three more steps reproduce `later`
+    path = snapshot.snapshot_path(str(tmp_path), 0)
+    snapshot.output_snap(path, snap, dt, cfg)
+    f2, t2, _, _ = snapshot.input_snap(path, cfg)
+    assert t2 == dt
+    g = GPU(cfg)
+    g.initialize_GPU(f2)
+    for _ in range(3):
+        _, t2 = g.time_step(f2, dt, False, t2)
+    again = np.empty_like(f)
+    g.copy_farray_from_GPU(again)
+    g.finalize_GPU()
+    assert np.array_equal(again, later)
 
 
 def test_zero_velocity_uniform_state_is_steady(oracle_mod):
