@@ -5,9 +5,8 @@
 // See include/pcb200.h for the contract and DESIGN.md for the data layout.
 #include "pcb200_device.cuh"
 #include "pcb200_fast.cuh"
-#include "pcb200_v3.cuh"
 #include "pcb200_v5.cuh"
-#include "pcb200_v8.cuh"
+#include "pcb200_v9.cuh"
 #include <cudaTypedefs.h>
 #include "../../include/pcb200.h"
 
@@ -392,9 +391,9 @@ struct State {
   double *host_f = nullptr; // retained Fortran f (gpu_astaroth.cc:2040-2059)
   CUtensorMap tmap[2];      // TMA descriptors of f[0], f[1] (kernel variant 2)
   CUtensorMap tmap_df;      // df tiles (32 x 8 x 1 x nvar) for L2 prefetch
-  CUtensorMap tmap3_ring[2], tmap3_scal[2]; // variant 3: 3-variable and {lnrho,ss} boxes
-  CUtensorMap tmap8_ring[2], tmap8_scal[2]; // variant 8: the same with (38 x 18) boxes
-  int variant = 1;          // kernel actually used (1 = global-load, 2 = smem ring + TMA, 3 = 2 + role split)
+  CUtensorMap tmap3_ring[2], tmap3_scal[2]; // variant 5: 3-variable and {lnrho,ss} boxes
+  CUtensorMap tmap9[2];     // variant 9: one (38 x 14 x 1 x nvar) box per plane
+  int variant = 1;          // kernel actually used (1 = global loads, 4 = TMA ring anisotropic, 5 = TMA ring isotropic, 9 = all-trail + TMEM)
   int nsm = 148;
   cudaStream_t stream = nullptr, comm_stream = nullptr;
   bool own_stream = false;
@@ -499,6 +498,7 @@ static void derive_pars() {
   P.lheatc_chiconst = c.lheatc_chiconst; P.lviscosity_heat = c.lviscosity_heat;
   P.lresi_eta_const = c.lresi_eta_const; P.lohmic_heat = c.lohmic_heat; P.llorentzforce = c.llorentzforce;
   P.lupw_uu = c.lupw_uu; P.lupw_lnrho = c.lupw_lnrho; P.lupw_ss = c.lupw_ss; P.lupw_aa = c.lupw_aa;
+  for (int i = 0; i < 3; ++i) P.dmcu[i] = c.lvisc_nu_const ? (c.nu * (1. / 3.)) * P.dmc[0][i] : 0.0;
 }
 
 static void check_supported() {
@@ -572,11 +572,11 @@ template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false> static voi
   rhs_update_v2<ENT, MAG, HYP, UPW, TRAIL><<<g, b, L::SMEM_BYTES, st>>>(tm, S.tmap_df, v);
 }
 
-template <bool ENT, bool MAG, bool HYP, bool UPW, int TM = 0> static void launch_update_v5(const UpdateArgs &a, cudaStream_t st) {
+template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v5(const UpdateArgs &a, cudaStream_t st) {
   typedef V5Layout<ENT, MAG> L;
   static bool attr_set = false;
   if (!attr_set) {
-    CK(cudaFuncSetAttribute(rhs_update_v5<ENT, MAG, HYP, UPW, TM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    CK(cudaFuncSetAttribute(rhs_update_v5<ENT, MAG, HYP, UPW, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
     attr_set = true;
   }
   V2Args v;
@@ -591,60 +591,42 @@ template <bool ENT, bool MAG, bool HYP, bool UPW, int TM = 0> static void launch
   nch = (nzr + v.lz - 1) / v.lz;
   dim3 g(gx, gy, nch), b(V2_TX, V2_TY, 1);
   const int w = (a.fin == S.f[0]) ? 0 : 1;
-  rhs_update_v5<ENT, MAG, HYP, UPW, TM><<<g, b, L::SMEM_BYTES, st>>>(S.tmap3_ring[w], S.tmap3_scal[w], v);
+  rhs_update_v5<ENT, MAG, HYP, UPW, 0><<<g, b, L::SMEM_BYTES, st>>>(S.tmap3_ring[w], S.tmap3_scal[w], v);
 }
 
-template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v8(const UpdateArgs &a, cudaStream_t st) {
-  typedef V8Layout<ENT, MAG> L;
+template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v9(const UpdateArgs &a, cudaStream_t st) {
+  constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
+  typedef V9Layout<NV> L;
   static bool attr_set = false;
   if (!attr_set) {
-    CK(cudaFuncSetAttribute(rhs_update_v8<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    CK(cudaFuncSetAttribute(rhs_update_v9<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
     attr_set = true;
   }
   V2Args v;
   v.fin = a.fin; v.fout = a.fout; v.df = a.df; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
   v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
-  v.df_prefetch = S.df_prefetch;
-  const int gx = (S.P.nx + V8_TX - 1) / V8_TX, gy = (S.P.ny + V8_TY - 1) / V8_TY;
+  v.df_prefetch = 0;
+  const int gx = (S.P.nx + V2_TX - 1) / V2_TX, gy = (S.P.ny + V2_TY - 1) / V2_TY;
   const int nzr = a.z_hi - a.z_lo;
-  int nch = (4 * S.nsm + gx * gy - 1) / (gx * gy);
-  { // one CTA per SM: among nch..nch+3 z chunks take the count whose last wave is fullest
+  // one CTA per SM; every z chunk pays 6 extra stages (3 warm-up + 3 cool-down, each ~1/4 of an evaluated plane):
+  // among the chunk counts that give at least one full wave take the one with the best (wave fill) x (chunk efficiency)
+  int pick = 1;
+  {
     double best = 0.0;
-    int pick = nch;
-    for (int c = nch; c < nch + 4; ++c) {
-      const double waves = (double)gx * gy * c / S.nsm, eff = waves / std::ceil(waves);
-      if (eff > best + 0.02) { best = eff; pick = c; }
+    const int tiles = gx * gy;
+    const int cmax = std::max(1, nzr / 8);
+    for (int c = 1; c <= cmax && tiles * c <= 16 * S.nsm; ++c) {
+      const int lz = (nzr + c - 1) / c;
+      const double waves = (double)tiles * ((nzr + lz - 1) / lz) / S.nsm;
+      const double eff = waves / std::ceil(waves) * (lz / (lz + 1.5));
+      if (eff > best + 0.01) { best = eff; pick = c; }
     }
-    nch = pick;
   }
-  nch = std::max(1, std::min(nch, std::max(1, nzr / 16)));
-  v.lz = (nzr + nch - 1) / nch;
-  nch = (nzr + v.lz - 1) / v.lz;
-  dim3 g(gx, gy, nch), b(V8_TX, V8_TY, 1);
+  v.lz = (nzr + pick - 1) / pick;
+  const int nch = (nzr + v.lz - 1) / v.lz;
+  dim3 g(gx, gy, nch), b(V2_TX, V2_TY, 1);
   const int w = (a.fin == S.f[0]) ? 0 : 1;
-  rhs_update_v8<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(S.tmap8_ring[w], S.tmap8_scal[w], v);
-}
-
-template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v3(const UpdateArgs &a, cudaStream_t st) {
-  typedef V3Layout<ENT, MAG> L;
-  static bool attr_set = false;
-  if (!attr_set) {
-    CK(cudaFuncSetAttribute(rhs_update_v3<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
-    attr_set = true;
-  }
-  V2Args v;
-  v.fin = a.fin; v.fout = a.fout; v.df = a.df; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
-  v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
-  v.df_prefetch = S.df_prefetch;
-  const int gx = (S.P.nx + V3_TX - 1) / V3_TX, gy = (S.P.ny + V3_TY - 1) / V3_TY;
-  const int nzr = a.z_hi - a.z_lo;
-  int nch = (4 * S.nsm + gx * gy - 1) / (gx * gy);
-  nch = std::max(1, std::min(nch, std::max(1, nzr / 16)));
-  v.lz = (nzr + nch - 1) / nch;
-  nch = (nzr + v.lz - 1) / v.lz;
-  dim3 g(gx, gy, nch), b(V3_TX, V3_TY, MAG ? 2 : 1);
-  const int w = (a.fin == S.f[0]) ? 0 : 1;
-  rhs_update_v3<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(S.tmap3_ring[w], S.tmap3_scal[w], v);
+  rhs_update_v9<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(S.tmap9[w], v);
 }
 
 static void launch_update(const UpdateArgs &a, cudaStream_t st) {
@@ -665,13 +647,9 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   }
 #define DISPATCH(E, M, H, U)                                   \
   do {                                                         \
-    if (S.variant == 8) launch_update_v8<E, M, H, U>(a, st); \
-    else if (S.variant == 7) launch_update_v5<E, M, H, U, 2>(a, st); \
-    else if (S.variant == 6) launch_update_v5<E, M, H, U, 1>(a, st); \
+    if (S.variant == 9) launch_update_v9<E, M, H, U>(a, st); \
     else if (S.variant == 5) launch_update_v5<E, M, H, U>(a, st);   \
     else if (S.variant == 4) launch_update_v2<E, M, H, U, true>(a, st); \
-    else if (S.variant == 3) launch_update_v3<E, M, H, U>(a, st);   \
-    else if (S.variant == 2) launch_update_v2<E, M, H, U>(a, st); \
     else launch_update_v1<E, M, H, U>(a, st);                  \
   } while (0)
   const int key = (ent ? 8 : 0) | (mag ? 4 : 0) | (hyp ? 2 : 0) | (upw ? 1 : 0);
@@ -1180,26 +1158,23 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   // kernel variant: TMA needs 16-byte global strides -> mx even
   const bool tma_ok = (P.mx % 2 == 0);
   const int kv = S.cfg.kernel_variant;
-  if (kv < 0 || kv > 8) die("kernel_variant=%d unknown (0 = auto, 1 ... 8)", kv);
+  if (kv != 0 && kv != 1 && kv != 4 && kv != 5 && kv != 9) die("kernel_variant=%d unknown (0 = auto, 1, 4, 5, 9)", kv);
   if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
   const bool iso = S.cfg.dx == S.cfg.dy && S.cfg.dy == S.cfg.dz; // variant 5 shares one set of stencil weights
-  S.variant = kv ? kv : (tma_ok ? (iso ? 5 : 4) : 1);
+  S.variant = kv ? kv : (tma_ok ? (iso ? 9 : 4) : 1);
   if (S.variant >= 5 && !iso) S.variant = 4; // anisotropic spacing: same kernel structure with per-direction weights
   if (S.variant >= 2) make_tensor_map(&S.tmap_df, S.df, V2_TX, V2_TY, P.nvar);
-  if (S.variant == 2 || S.variant == 4) {
+  if (S.variant == 4) {
     make_tensor_map(&S.tmap[0], S.f[0]);
     make_tensor_map(&S.tmap[1], S.f[1]);
   }
-  if (S.variant == 3 || S.variant >= 5) {
-    for (int w = 0; w < 2; ++w) {
-      make_tensor_map(&S.tmap3_ring[w], S.f[w], V3_HX, V3_HY, 3);
-      make_tensor_map(&S.tmap3_scal[w], S.f[w], V3_HX, V3_HY, S.cfg.iss >= 0 ? 2 : 1);
-    }
+  if (S.variant == 9) {
+    for (int w = 0; w < 2; ++w) make_tensor_map(&S.tmap9[w], S.f[w], V2_HX, V2_HY, P.nvar);
   }
-  if (S.variant == 8) {
+  if (S.variant == 5) {
     for (int w = 0; w < 2; ++w) {
-      make_tensor_map(&S.tmap8_ring[w], S.f[w], V8_HX, V8_HY, 3);
-      make_tensor_map(&S.tmap8_scal[w], S.f[w], V8_HX, V8_HY, S.cfg.iss >= 0 ? 2 : 1);
+      make_tensor_map(&S.tmap3_ring[w], S.f[w], V2_HX, V2_HY, 3);
+      make_tensor_map(&S.tmap3_scal[w], S.f[w], V2_HX, V2_HY, S.cfg.iss >= 0 ? 2 : 1);
     }
   }
   // halo machinery: yz-pencils need y-face staging; z exchange is overlapped with the interior kernel

@@ -35,6 +35,7 @@ struct Pars {
   double d1c[3][3];     // d1fac * (45, -9, 1)
   double d2c[3][4];     // d2fac * (-490, 270, -27, 2)/180
   double dmc[3][3];     // dmfac * (270, -27, 2)
+  double dmcu[3];       // (nu/3) * dmc[0][:] (variant 9: z-mixed part of grad div u scattered straight into du/dt)
   double d2c0x2, d2c0x3; // 2x / 3x the centre weight of der2 (isotropic grids: second derivatives summed over directions)
   double dline_1[3];
   double dxyz_2, dxyz_4, dxyz_6;

@@ -1,0 +1,647 @@
+// pcb200_v9.cuh -- kernel variant 9: z-marching with "all-trail" z-mixed derivatives and delayed finalisation.
+//
+// What changed against variant 5 (profiles/r01_v5_ncu_full_256.txt: 228 LDS.64 + 655 FP64 + 1270 issue slots per
+// cell, shared-memory pipe 74 % busy at 8 warps per SM):
+//   * all variables are staged alike: ONE TMA box (38 x 14 x 1 x nvar) per xy-plane into a 6-slot shared-memory
+//     ring (planes z..z+3 in use, two in flight); only the centre plane is read for in-plane taps, the plane z+3
+//     only for the thread's own column (the newest entry of its z history);
+//   * the own-column z taps f(z-3..z+2) of every variable live in tensor memory (TMEM, tcgen05.ld/st: per-thread
+//     columns), 6 doubles per variable, shifted by one entry per plane with 2-column stores straight from the loaded
+//     registers (wider stores would need re-packed, aligned register blocks) -- no register pipelines, no ring reads;
+//   * the z-mixed bidiagonal derivatives (deriv.f90:1400-1452)
+//        d_zx f(z) = sum_k w_k [Dx_k f(z+k) - Dx_k f(z-k)],   Dx_k f(z') = f(x+k,y,z') - f(x-k,y,z')
+//     are never gathered: when plane z' is the centre plane the differences Dx_k, Dy_k that its first derivatives
+//     form anyway are scattered into the accumulators of the six output planes z'-3..z'+3 ("trail" for the later
+//     planes, as in variant 4/5, and now also for the EARLIER planes, which replaces the 48 "lead" loads and 48 FP64
+//     operations per cell).  The price: the terms that contain them -- grad div u in the viscous force, the current
+//     density j = curl curl A / mu0 in the Lorentz force and the Ohmic heating -- are complete three planes late, so
+//     u (and s when there is a magnetic field) of plane z-3 are finalised and written while plane z is evaluated;
+//     what they need besides the accumulators (b, 1/rho, eta mu0/(rho T), the partial ds/dt) waits in TMEM.
+//     The accumulators themselves are a circular TMEM ring indexed by output plane (8 slots of 16 columns, updated by
+//     read-modify-write with a dynamic column address): no registers are held and nothing is shifted.
+//     Every z chunk therefore runs 3 warm-up and 3 cool-down stages that only form the in-plane differences.
+// Isotropic grids only (dx == dy == dz); arithmetic and reference citations: pcb200_device.cuh / pcb200_fast.cuh.
+#pragma once
+#include "pcb200_fast.cuh"
+
+namespace pcb200 {
+
+constexpr int V9_NSLOT = 6; // planes z..z+3 in use + 2 in flight
+
+template <int NV> struct V9Layout {
+  static constexpr int SLOT = ((NV * V2_PLANE + 15) / 16) * 16; // doubles per slot (TMA destination: 128-byte aligned)
+  static constexpr unsigned TX_BYTES = NV * V2_PLANE * 8;
+  static constexpr size_t SMEM_BYTES = (size_t)V9_NSLOT * SLOT * 8 + V9_NSLOT * 8 + 64;
+};
+
+// ---- tensor memory as per-thread scratch (shape 32x32b: lane = thread, 32-bit columns).  No "memory" clobber: TMEM
+// is invisible to every other memory operation of the kernel, so shared/global loads may be scheduled across these
+// blocks; `volatile` keeps the tcgen05 operations in program order among themselves and each load block contains
+// its own wait, so no result can be used early.
+__device__ __forceinline__ void t9_ld6(uint32_t taddr, double h[6]) { // columns 0..11
+  asm volatile(
+      "{\n\t.reg .b32 t<12>;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {t0, t1, t2, t3, t4, t5, t6, t7}, [%6];\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x4.b32 {t8, t9, t10, t11}, [%7];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 %0, {t0, t1};\n\tmov.b64 %1, {t2, t3};\n\tmov.b64 %2, {t4, t5};\n\t"
+      "mov.b64 %3, {t6, t7};\n\tmov.b64 %4, {t8, t9};\n\tmov.b64 %5, {t10, t11};\n\t}"
+      : "=d"(h[0]), "=d"(h[1]), "=d"(h[2]), "=d"(h[3]), "=d"(h[4]), "=d"(h[5])
+      : "r"(taddr), "r"(taddr + 8));
+}
+__device__ __forceinline__ void t9_ld8(uint32_t taddr, double h[8]) { // columns 0..15
+  asm volatile(
+      "{\n\t.reg .b32 t<16>;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {t0, t1, t2, t3, t4, t5, t6, t7, t8, t9, t10, t11, t12, t13, t14, t15}, [%8];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 %0, {t0, t1};\n\tmov.b64 %1, {t2, t3};\n\tmov.b64 %2, {t4, t5};\n\tmov.b64 %3, {t6, t7};\n\t"
+      "mov.b64 %4, {t8, t9};\n\tmov.b64 %5, {t10, t11};\n\tmov.b64 %6, {t12, t13};\n\tmov.b64 %7, {t14, t15};\n\t}"
+      : "=d"(h[0]), "=d"(h[1]), "=d"(h[2]), "=d"(h[3]), "=d"(h[4]), "=d"(h[5]), "=d"(h[6]), "=d"(h[7])
+      : "r"(taddr));
+}
+__device__ __forceinline__ double t9_ld1(uint32_t taddr) { // columns 0..1
+  double v;
+  asm volatile(
+      "{\n\t.reg .b32 t<2>;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x2.b32 {t0, t1}, [%1];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 %0, {t0, t1};\n\t}"
+      : "=d"(v)
+      : "r"(taddr));
+  return v;
+}
+__device__ __forceinline__ void t9_st4(uint32_t taddr, double a, double b, double c, double d) { // columns 0..7
+  asm volatile(
+      "{\n\t.reg .b32 t<8>;\n\tmov.b64 {t0, t1}, %1;\n\tmov.b64 {t2, t3}, %2;\n\tmov.b64 {t4, t5}, %3;\n\tmov.b64 {t6, t7}, %4;\n\t"
+      "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {t0, t1, t2, t3, t4, t5, t6, t7};\n\t}" ::"r"(taddr),
+      "d"(a), "d"(b), "d"(c), "d"(d));
+}
+__device__ __forceinline__ void t9_st2(uint32_t taddr, double a, double b) { // columns 0..3
+  asm volatile(
+      "{\n\t.reg .b32 t<4>;\n\tmov.b64 {t0, t1}, %1;\n\tmov.b64 {t2, t3}, %2;\n\t"
+      "tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {t0, t1, t2, t3};\n\t}" ::"r"(taddr),
+      "d"(a), "d"(b));
+}
+__device__ __forceinline__ void t9_st1(uint32_t taddr, double a) { // columns 0..1
+  asm volatile("{\n\t.reg .b32 t<2>;\n\tmov.b64 {t0, t1}, %1;\n\ttcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {t0, t1};\n\t}" ::"r"(taddr), "d"(a));
+}
+__device__ __forceinline__ void t9_st8(uint32_t taddr, const double h[8]) { // columns 0..15
+  asm volatile(
+      "{\n\t.reg .b32 t<16>;\n\tmov.b64 {t0, t1}, %1;\n\tmov.b64 {t2, t3}, %2;\n\tmov.b64 {t4, t5}, %3;\n\tmov.b64 {t6, t7}, %4;\n\t"
+      "mov.b64 {t8, t9}, %5;\n\tmov.b64 {t10, t11}, %6;\n\tmov.b64 {t12, t13}, %7;\n\tmov.b64 {t14, t15}, %8;\n\t"
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {t0, t1, t2, t3, t4, t5, t6, t7, t8, t9, t10, t11, t12, t13, t14, t15};\n\t}" ::"r"(taddr),
+      "d"(h[0]), "d"(h[1]), "d"(h[2]), "d"(h[3]), "d"(h[4]), "d"(h[5]), "d"(h[6]), "d"(h[7]));
+}
+// two 16-column loads behind one wait
+__device__ __forceinline__ void t9_ld8x2(uint32_t ta, uint32_t tb, double h[8], double g[8]) {
+  asm volatile(
+      "{\n\t.reg .b32 t<32>;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {t0, t1, t2, t3, t4, t5, t6, t7, t8, t9, t10, t11, t12, t13, t14, t15}, [%16];\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {t16, t17, t18, t19, t20, t21, t22, t23, t24, t25, t26, t27, t28, t29, t30, t31}, [%17];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 %0, {t0, t1};\n\tmov.b64 %1, {t2, t3};\n\tmov.b64 %2, {t4, t5};\n\tmov.b64 %3, {t6, t7};\n\t"
+      "mov.b64 %4, {t8, t9};\n\tmov.b64 %5, {t10, t11};\n\tmov.b64 %6, {t12, t13};\n\tmov.b64 %7, {t14, t15};\n\t"
+      "mov.b64 %8, {t16, t17};\n\tmov.b64 %9, {t18, t19};\n\tmov.b64 %10, {t20, t21};\n\tmov.b64 %11, {t22, t23};\n\t"
+      "mov.b64 %12, {t24, t25};\n\tmov.b64 %13, {t26, t27};\n\tmov.b64 %14, {t28, t29};\n\tmov.b64 %15, {t30, t31};\n\t}"
+      : "=d"(h[0]), "=d"(h[1]), "=d"(h[2]), "=d"(h[3]), "=d"(h[4]), "=d"(h[5]), "=d"(h[6]), "=d"(h[7]), "=d"(g[0]), "=d"(g[1]),
+        "=d"(g[2]), "=d"(g[3]), "=d"(g[4]), "=d"(g[5]), "=d"(g[6]), "=d"(g[7])
+      : "r"(ta), "r"(tb));
+}
+__device__ __forceinline__ void t9_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;"); }
+
+// taps of one line: m[i] / p[i] at -(i+1) / +(i+1) along x, y (shared memory, centre plane) or z (TMEM history)
+__device__ __forceinline__ void v9_xline(const double *q, double m[3], double p[3]) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    m[i] = q[-(i + 1)];
+    p[i] = q[i + 1];
+  }
+}
+__device__ __forceinline__ void v9_yline(const double *q, double m[3], double p[3]) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    m[i] = q[-(i + 1) * V2_HX];
+    p[i] = q[(i + 1) * V2_HX];
+  }
+}
+__device__ __forceinline__ void v9_zline(const double h[7], double m[3], double p[3]) { // h = f(z-3..z+3)
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    m[i] = h[2 - i];
+    p[i] = h[4 + i];
+  }
+}
+// bidiagonal xy derivative in the centre plane (deriv.f90:1400-1452)
+__device__ __forceinline__ double v9_dxy(const double *q) {
+  double g[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const int a = (i + 1), b = (i + 1) * V2_HX;
+    g[i] = (q[a + b] - q[-a + b]) + (q[-a - b] - q[a - b]);
+  }
+  return cP.dmc[0][0] * g[0] + (cP.dmc[0][1] * g[1] + cP.dmc[0][2] * g[2]);
+}
+
+extern __shared__ __align__(1024) double v9_smem[];
+
+template <bool ENT, bool MAG, bool HYP, bool UPW>
+__global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_constant__ CUtensorMap tmap, const V2Args a) {
+  typedef Slots<ENT> S;
+  constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
+  constexpr int NGRP = MAG ? 2 : 1;   // vector fields with a grad div: u (and A)
+  constexpr bool SDEL = ENT && MAG;   // ds/dt contains the Ohmic heating -> finalised three planes late as well
+  typedef V9Layout<NV> L;
+  const Pars &P = cP;
+
+  double *planes = v9_smem;
+  uint64_t *bars = reinterpret_cast<uint64_t *>(planes + V9_NSLOT * L::SLOT);
+  uint32_t *tm_slot = reinterpret_cast<uint32_t *>(bars + V9_NSLOT);
+
+  const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * V2_TX + tx;
+  const int bx0 = blockIdx.x * V2_TX, by0 = blockIdx.y * V2_TY; // origin of the halo'd tile (incl. ghosts)
+  const int zc0 = a.z_lo + blockIdx.z * a.lz;
+  const int zc1 = min(zc0 + a.lz, a.z_hi);
+  if (zc0 >= zc1) return;
+  const int nst = (zc1 - zc0) + 2 * NG; // stages: centre planes zc0-3 .. zc1+2
+  const int ix = bx0 + tx + NG, iy = by0 + ty + NG;
+  const bool active = ix < P.nx + NG && iy < P.ny + NG;
+  const int ixc = min(ix, P.nx + NG - 1), iyc = min(iy, P.ny + NG - 1);
+
+  if (tid == 0) {
+    if (smem_u32(planes) & 127u) __trap();
+    for (int s = 0; s < V9_NSLOT; ++s) mbar_init(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  if (tid < 32) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tm_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+  auto issue = [&](int j) { // stage j <-> plane zc0-3+j, slot j % 6
+    if (j >= nst) return;
+    const int s = j % V9_NSLOT;
+    mbar_expect_tx(&bars[s], L::TX_BYTES);
+    tma_load_4d(planes + s * L::SLOT, &tmap, &bars[s], bx0, by0, zc0 - NG + j, 0);
+  };
+  if (tid == 0) {
+#pragma unroll 1
+    for (int j = 0; j < V9_NSLOT; ++j) issue(j);
+  }
+
+  // TMEM columns of this thread (two warps share each lane quarter -> 256 columns each):
+  //   [0,96)    z histories: variable k at 12k, entries f(z-3..z+2)
+  //   [96,224)  accumulator ring: the output plane of stage index i owns the 16 columns at 96 + 16 (i & 7):
+  //             {U0, U1, U2, -, A0, A1, A2, -}: sums for du/dt (scaled by nu/3) and for mu0 j;
+  //             U3 / A3 carry 1/rho and eta mu0/(rho T) of the plane from its centre stage on
+  //   [224,256) {partial ds/dt, b_x, b_y, b_z} of the planes z-3..z: stage index i at 224 + 8 (i & 3)
+  const uint32_t tmb = *tm_slot + ((uint32_t)((tid >> 5) & 3) << 21) + (uint32_t)(tid >> 7) * 256u;
+  const uint32_t tmh = tmb, tma = tmb + 96u, tmp = tmb + 224u;
+
+  const int toff = (ty + NG) * V2_HX + (tx + NG);
+  const long long sv = P.sv, sz = P.sz;
+  const long long col = ixc + P.sy * iyc;
+  { // z histories of the first evaluated plane zc0: own column, planes zc0-3..zc0+2 (coalesced global loads)
+    const double *g = a.fin + col + sz * (zc0 - NG);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      double h[6];
+#pragma unroll
+      for (int d = 0; d < 6; ++d) h[d] = __ldg(g + k * sv + sz * d);
+      t9_st4(tmh + 12u * k, h[0], h[1], h[2], h[3]);
+      t9_st2(tmh + 12u * k + 8u, h[4], h[5]);
+    }
+  }
+
+  const double dtb = (*a.dt_dev) * a.beta;
+  const bool rdf = a.read_df != 0 && active;
+  // running pointers (advance by one plane per stage): cell (ix, iy) of the centre plane of the stage, variable 0
+  const long long o0 = ix + P.sy * iy + sz * (zc0 - NG);
+  double *pdf = a.df + o0, *pfo = a.fout + o0;
+  double fxy_r = 0.0, fxy_i = 0.0; // helical forcing: fx(x)*fy(y) of this thread
+  if (a.frc.on) {
+    const double2 fx = a.frc.fx[ixc], fy = a.frc.fy[iyc];
+    fxy_r = fx.x * fy.x - fx.y * fy.y;
+    fxy_i = fx.x * fy.y + fx.y * fy.x;
+  }
+  // 2N-RK3 update of one variable (timestep.f90:113,160-161); off = offset from the running pointers
+  auto rk = [&](double r, double dfo, double fcv, long long off, double extra) {
+    const double d = a.alpha * dfo + r;
+    if (a.write_df) __stcs(pdf + off, d);
+    pfo[off] = (fcv + dtb * d) + extra;
+  };
+
+  int slot = 0, par = 0;
+#pragma unroll 1
+  for (int j = 0; j < nst; ++j) {
+    const bool full = j >= NG && j < nst - NG; // centre plane inside [zc0, zc1): evaluate it
+    const bool fin = j >= 2 * NG;              // plane (centre - 3) >= zc0: finalise it
+    // slot release + TMA issue: the first warp waits until every warp has finished stage j-1, then refills its slot.
+    // Eight rotating named barriers: a warp can be at most 5 stages ahead of the slowest one.
+    if (tid < 32 && j > 0) {
+      named_bar_sync(1 + ((j - 1) & 7), V2_THREADS);
+      if (tid == 0) issue(j - 1 + V9_NSLOT);
+      __syncwarp();
+    }
+    // early global loads: df of the planes written in this stage
+    double dfv[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const bool del = (k < 3) || (SDEL && k == S::ISS);
+      const bool on = rdf && (del ? fin : full);
+      dfv[k] = on ? __ldg(pdf + k * sv - (del ? NG * sz : 0)) : 0.0;
+    }
+    double2 fzv = make_double2(0.0, 0.0);
+    if (a.frc.on && fin) fzv = __ldg(a.frc.fz + (zc0 - 2 * NG + j));
+
+    mbar_wait(&bars[slot], par);
+    const double *cp = planes + slot * L::SLOT + toff;
+    t9_wait_st(); // TMEM stores of the previous stage are complete
+
+    // in-plane differences of this plane: Eg[g][c][k-1], c = 0: Dx_k f_z, 1: Dy_k f_z, 2: Dx_k f_x + Dy_k f_y
+    double Eg[NGRP][3][3];
+    double part[NGRP][3];            // centre plane: everything else of du/dt (g = 0) and of mu0 j (g = 1)
+    double rho1 = 0.0, hT = 0.0;     // 1/rho and eta mu0/(rho T) of the centre plane
+    double fq[4] = {0., 0., 0., 0.}; // f(centre - 3) of the variables that are finalised late
+#pragma unroll
+    for (int g = 0; g < NGRP; ++g)
+#pragma unroll
+      for (int c = 0; c < 3; ++c) part[g][c] = 0.0;
+
+    if (full) {
+      const int slot3 = slot + 3 >= V9_NSLOT ? slot + 3 - V9_NSLOT : slot + 3;
+      mbar_wait(&bars[slot3], slot + 3 >= V9_NSLOT ? par ^ 1 : par);
+      const double *cp3 = planes + slot3 * L::SLOT + toff;
+      // z history of variable k: f(z-3..z+2) from TMEM, f(z+3) from the newest plane; stored back shifted by one
+      auto hist = [&](int k, double h[7]) {
+        const uint32_t ta = tmh + 12u * k;
+        t9_ld6(ta, h);
+        h[6] = cp3[k * V2_PLANE];
+#pragma unroll
+        for (int e = 0; e < 6; ++e) t9_st1(ta + 2u * e, h[e + 1]);
+      };
+      double h[7], m[3], pp[3], dxx[3];
+      double au[3] = {0., 0., 0.};
+      if (UPW) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) au[i] = fabs(cp[(S::IUX + i) * V2_PLANE]);
+      }
+      const bool hyp_visc = HYP && (P.lvisc_hyper3_simplified || P.lvisc_hyper3_nu_const);
+
+      // ---------------- lnrho (density.f90:2727-2811)
+      hist(S::ILN, h);
+      const double lnrho = h[3];
+      double gl[3], del2lnrho = 0.0, del6lnrho = 0.0, upw_l = 0.0;
+      {
+        SymSum sl;
+#pragma unroll
+        for (int jd = 0; jd < 3; ++jd) {
+          if (jd == 0) v9_xline(cp + S::ILN * V2_PLANE, m, pp);
+          else if (jd == 1) v9_yline(cp + S::ILN * V2_PLANE, m, pp);
+          else v9_zline(h, m, pp);
+          gl[jd] = d1_line(m, pp, 0);
+          if (ENT) sl.add(m, pp);
+          if (HYP || UPW) {
+            const double r6 = d6raw_line(lnrho, m, pp);
+            if (HYP) del6lnrho += P.d6fac[0] * r6;
+            if (UPW) upw_l += au[jd] * (P.d6upfac[0] * r6);
+          }
+        }
+        if (ENT) del2lnrho = sl.weighted(lnrho, P.d2c0x3);
+      }
+
+      // ---------------- velocity (hydro.f90:3925-4063, sub.f90:2610-2749)
+      double u[3], uij[3][3], del2u[3], gdu[3], hyp[3] = {0., 0., 0.}, upw_u[3] = {0., 0., 0.};
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        hist(S::IUX + i, h);
+        u[i] = h[3];
+        fq[i] = h[0];
+        const double *q = cp + (S::IUX + i) * V2_PLANE;
+        double d2s = 0.0;
+        SymSum su;
+#pragma unroll
+        for (int jd = 0; jd < 3; ++jd) {
+          if (jd == 0) v9_xline(q, m, pp);
+          else if (jd == 1) v9_yline(q, m, pp);
+          else v9_zline(h, m, pp);
+          uij[i][jd] = d1_line(m, pp, 0);
+          // in-plane differences of this plane feed the z-mixed sums of the planes z-3..z+3
+          if (i == 2 && jd == 0) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) Eg[0][0][k] = pp[k] - m[k];
+          }
+          if (i == 2 && jd == 1) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) Eg[0][1][k] = pp[k] - m[k];
+          }
+          if (i == 0 && jd == 0) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) dxx[k] = pp[k] - m[k];
+          }
+          if (i == 1 && jd == 1) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) Eg[0][2][k] = dxx[k] + (pp[k] - m[k]);
+          }
+          if (jd != i) {
+            su.add(m, pp); // the two off-diagonal second derivatives only enter through their sum
+          } else {
+            const double d2 = d2_line(u[i], m, pp, 0);
+            d2s += d2;
+            gdu[i] = d2; // fjji(i,i)=der2 (sub.f90:2651-2653)
+          }
+          if (HYP || UPW) {
+            const double r6 = d6raw_line(u[i], m, pp);
+            if (HYP) {
+              hyp[i] += P.d6fac[0] * r6;                                       // del6v
+              if (P.lvisc_hyper3_nu_const) hyp[i] += d5_line(m, pp, 0) * gl[jd]; // uij5glnrho
+            }
+            if (UPW) upw_u[i] += au[jd] * (P.d6upfac[0] * r6);
+          }
+        }
+        d2s += su.weighted(u[i], P.d2c0x2);
+        del2u[i] = d2s;
+      }
+      // xy parts of grad div u (the z-mixed parts arrive through the accumulator ring)
+      gdu[0] += v9_dxy(cp + (S::IUX + 1) * V2_PLANE);
+      gdu[1] += v9_dxy(cp + (S::IUX + 0) * V2_PLANE);
+
+      const double divu = uij[0][0] + uij[1][1] + uij[2][2];
+      double sij[3][3];
+#pragma unroll
+      for (int jd = 0; jd < 3; ++jd) {
+        sij[jd][jd] = uij[jd][jd] - (1. / 3.) * divu;
+#pragma unroll
+        for (int i = jd + 1; i < 3; ++i) {
+          sij[i][jd] = .5 * (uij[i][jd] + uij[jd][i]);
+          sij[jd][i] = sij[i][jd];
+        }
+      }
+      double ru[3];
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        double ugu = u[0] * uij[i][0] + u[1] * uij[i][1] + u[2] * uij[i][2];
+        if (UPW && P.lupw_uu) ugu -= upw_u[i];
+        ru[i] = -ugu;
+      }
+      double uglnrho = u[0] * gl[0] + u[1] * gl[1] + u[2] * gl[2];
+      if (UPW && P.lupw_lnrho) uglnrho -= upw_l;
+      // viscosity (viscosity.f90:1633-1664, :1982-1989, :2250-2257)
+      double sij2 = 0.0;
+      if (P.lvisc_nu_const) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          const double sgl = sij[i][0] * gl[0] + sij[i][1] * gl[1] + sij[i][2] * gl[2];
+          ru[i] += P.nu * (del2u[i] + 2. * sgl + (1. / 3.) * gdu[i]);
+        }
+        if (ENT) {
+          sij2 = sij[0][0] * sij[0][0] + sij[1][1] * sij[1][1] + sij[2][2] * sij[2][2] +
+                 2 * (sij[1][0] * sij[1][0] + sij[2][0] * sij[2][0] + sij[2][1] * sij[2][1]);
+        }
+      }
+      if (hyp_visc) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) ru[i] += P.nu_hyper3 * hyp[i];
+      }
+      // continuity (density.f90:2887-3060, 3197-3288)
+      double rl = (-divu) - uglnrho;
+      if (HYP && P.ldiff_hyper3lnrho) rl += P.diffrho_hyper3 * del6lnrho;
+      if (active) rk(rl, dfv[S::ILN], lnrho, S::ILN * sv, 0.0);
+
+      // eos + energy (eos_idealgas.f90:851-888, entropy.f90:3554-3876, 4852-4947)
+      double rs = 0.0, TT1 = 0.0;
+      if (ENT) {
+        hist(S::ISS, h);
+        const double ss = h[3];
+        fq[3] = h[0];
+        double gss[3], del2ss = 0.0, upw_s = 0.0;
+        SymSum sss;
+#pragma unroll
+        for (int jd = 0; jd < 3; ++jd) {
+          if (jd == 0) v9_xline(cp + S::ISS * V2_PLANE, m, pp);
+          else if (jd == 1) v9_yline(cp + S::ISS * V2_PLANE, m, pp);
+          else v9_zline(h, m, pp);
+          gss[jd] = d1_line(m, pp, 0);
+          sss.add(m, pp);
+          if (UPW) upw_s += au[jd] * (P.d6upfac[0] * d6raw_line(ss, m, pp));
+        }
+        del2ss = sss.weighted(ss, P.d2c0x3);
+        const double e = P.cv1 * ss + P.gamma_m1 * (lnrho - P.lnrho0);
+        const double ex = exp_fast(e);
+        const double cs2 = P.cs20 * ex;
+        TT1 = P.TT0_1 * __drcp_rn(ex);
+        double g2 = 0.0;
+#pragma unroll
+        for (int jd = 0; jd < 3; ++jd) {
+          const double glnTT = P.gamma_m1 * gl[jd] + P.cv1 * gss[jd];
+          ru[jd] += -cs2 * (gl[jd] + glnTT) * P.gamma1;
+          g2 += (gl[jd] + glnTT) * glnTT;
+        }
+        double ugss = u[0] * gss[0] + u[1] * gss[1] + u[2] * gss[2];
+        if (UPW && P.lupw_ss) ugss -= upw_s;
+        rs = -ugss;
+        if (P.lviscosity_heat) rs += TT1 * (2 * P.nu * sij2);
+        if (P.lheatc_chiconst) rs += P.chi * P.cp * ((P.gamma_m1 * del2lnrho + P.cv1 * del2ss) + g2);
+        if (!SDEL && active) rk(rs, dfv[S::ISS], ss, S::ISS * sv, 0.0);
+      } else {
+#pragma unroll
+        for (int jd = 0; jd < 3; ++jd) ru[jd] += -P.cs20 * gl[jd];
+      }
+      // everything of du/dt except the z-mixed part of grad div u and the Lorentz force
+#pragma unroll
+      for (int c = 0; c < 3; ++c) part[0][c] = ru[c];
+
+      // ---------------- magnetic (magnetic.f90:4279-5225, 5392-6640)
+      if (MAG) {
+        const bool upa = UPW && P.lupw_aa;
+        double aij[3][3], dia[3], rest[3], upw_a[3] = {0., 0., 0.}, av[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          hist(S::IAX + i, h);
+          av[i] = h[3];
+          const double *q = cp + (S::IAX + i) * V2_PLANE;
+          SymSum sa;
+#pragma unroll
+          for (int jd = 0; jd < 3; ++jd) {
+            if (jd == 0) v9_xline(q, m, pp);
+            else if (jd == 1) v9_yline(q, m, pp);
+            else v9_zline(h, m, pp);
+            if (i == 2 && jd == 0) {
+#pragma unroll
+              for (int k = 0; k < 3; ++k) Eg[NGRP - 1][0][k] = pp[k] - m[k];
+            }
+            if (i == 2 && jd == 1) {
+#pragma unroll
+              for (int k = 0; k < 3; ++k) Eg[NGRP - 1][1][k] = pp[k] - m[k];
+            }
+            if (i == 0 && jd == 0) {
+#pragma unroll
+              for (int k = 0; k < 3; ++k) dxx[k] = pp[k] - m[k];
+            }
+            if (i == 1 && jd == 1) {
+#pragma unroll
+              for (int k = 0; k < 3; ++k) Eg[NGRP - 1][2][k] = dxx[k] + (pp[k] - m[k]);
+            }
+            aij[i][jd] = (i != jd || upa) ? d1_line(m, pp, 0) : 0.0;
+            if (jd == i) dia[i] = d2_line(av[i], m, pp, 0);
+            else sa.add(m, pp);
+            if (UPW && jd != i) upw_a[i] += au[jd] * (P.d6upfac[0] * d6raw_line(av[i], m, pp)); // mask=i (magnetic.f90:6301)
+          }
+          rest[i] = sa.weighted(av[i], P.d2c0x2);
+        }
+        const double bb[3] = {aij[2][1] - aij[1][2], aij[0][2] - aij[2][0], aij[1][0] - aij[0][1]};
+        // mu0 j = grad div A - del2 A: everything but the z-mixed parts
+        part[NGRP - 1][0] = v9_dxy(cp + (S::IAX + 1) * V2_PLANE) - rest[0];
+        part[NGRP - 1][1] = v9_dxy(cp + (S::IAX + 0) * V2_PLANE) - rest[1];
+        part[NGRP - 1][2] = -rest[2];
+        double fres[3] = {0., 0., 0.};
+        if (P.lresi_eta_const) {
+#pragma unroll
+          for (int i = 0; i < 3; ++i) fres[i] = P.eta * (dia[i] + rest[i]);
+        }
+        double ra[3];
+        if (!upa) { // dAdt = uxb + fres (magnetic.f90:6247)
+          ra[0] = (u[1] * bb[2] - u[2] * bb[1]) + fres[0];
+          ra[1] = (u[2] * bb[0] - u[0] * bb[2]) + fres[1];
+          ra[2] = (u[0] * bb[1] - u[1] * bb[0]) + fres[2];
+        } else { // upwinded induction (magnetic.f90:6257-6313)
+#pragma unroll
+          for (int jd = 0; jd < 3; ++jd) {
+            double x = 0.0;
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+              if (k != jd) x += u[k] * (aij[k][jd] - aij[jd][k]);
+            ra[jd] = (x + upw_a[jd]) + fres[jd];
+          }
+        }
+        if (active) {
+#pragma unroll
+          for (int i = 0; i < 3; ++i) rk(ra[i], dfv[S::IAX + i], av[i], (S::IAX + i) * sv, 0.0);
+        }
+        // what the Lorentz force and the Ohmic heating of this plane need three stages from now
+        rho1 = exp_fast(-lnrho); // density.f90:2750
+        hT = (ENT && P.lohmic_heat) ? P.eta * P.mu0 * rho1 * TT1 : 0.0;
+        t9_st4(tmp + 8u * (uint32_t)(j & 3), rs, bb[0], bb[1], bb[2]);
+      }
+    } else {
+      // warm-up / cool-down stage: only the in-plane differences of this plane
+      double m[3], pp[3], d[3];
+#pragma unroll
+      for (int g = 0; g < NGRP; ++g) {
+        const double *q = cp + (g == 0 ? S::IUX : S::IAX) * V2_PLANE;
+        v9_xline(q + 2 * V2_PLANE, m, pp);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) Eg[g][0][k] = pp[k] - m[k];
+        v9_yline(q + 2 * V2_PLANE, m, pp);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) Eg[g][1][k] = pp[k] - m[k];
+        v9_xline(q, m, pp);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) d[k] = pp[k] - m[k];
+        v9_yline(q + V2_PLANE, m, pp);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) Eg[g][2][k] = d[k] + (pp[k] - m[k]);
+      }
+      if (fin) { // cool-down: the histories stopped at planes zc1-3..zc1+2
+        const uint32_t e = 2u * (uint32_t)(j - (nst - NG));
+#pragma unroll
+        for (int i = 0; i < 3; ++i) fq[i] = t9_ld1(tmh + 12u * (S::IUX + i) + e);
+        if (SDEL) fq[3] = t9_ld1(tmh + 12u * S::ISS + e);
+      }
+    }
+
+    // ---------------- accumulator ring: this plane is z+k of the output planes z = centre-k and z-k of centre+k
+    //   sum_k w_k [E_k(z+k) - E_k(z-k)]  ->  slot(centre-k) += w_k E_k,  slot(centre+k) -= w_k E_k
+    double sA[8], sB[8];
+    const double wu[3] = {P.dmcu[0], P.dmcu[1], P.dmcu[2]}, wa[3] = {P.dmc[0][0], P.dmc[0][1], P.dmc[0][2]};
+    auto slot_of = [&](int d) { return tma + 16u * (uint32_t)((j + d) & 7); };
+    auto upd = [&](double s[8], int k, double sign) { // k = 1..3
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        s[c] = fma(sign * wu[k - 1], Eg[0][c][k - 1], s[c]);
+        if (MAG) s[4 + c] = fma(sign * wa[k - 1], Eg[NGRP - 1][c][k - 1], s[4 + c]);
+      }
+    };
+    // planes centre-3 (complete after this update) and centre-2
+    t9_ld8x2(slot_of(-3), slot_of(-2), sA, sB);
+    upd(sA, 3, 1.0);
+    upd(sB, 2, 1.0);
+    t9_st8(slot_of(-2), sB);
+    double rr[3] = {sA[0], sA[1], sA[2]};
+    const double jq[3] = {P.mu01 * sA[4], P.mu01 * sA[5], P.mu01 * sA[6]};
+    const double rho1q = sA[3], hTq = sA[7];
+    // planes centre-1 and centre (the centre plane adds its own part)
+    t9_ld8x2(slot_of(-1), slot_of(0), sA, sB);
+    upd(sA, 1, 1.0);
+    t9_st8(slot_of(-1), sA);
+    if (full) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        sB[c] += part[0][c];
+        if (MAG) sB[4 + c] += part[NGRP - 1][c];
+      }
+      sB[3] = rho1;
+      sB[7] = hT;
+      t9_st8(slot_of(0), sB);
+    }
+    // planes centre+1, centre+2 and the new plane centre+3
+    t9_ld8x2(slot_of(1), slot_of(2), sA, sB);
+    upd(sA, 1, -1.0);
+    upd(sB, 2, -1.0);
+    t9_st8(slot_of(1), sA);
+    t9_st8(slot_of(2), sB);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      sA[c] = -wu[2] * Eg[0][c][2];
+      sA[4 + c] = MAG ? -wa[2] * Eg[NGRP - 1][c][2] : 0.0;
+    }
+    sA[3] = 0.0;
+    sA[7] = 0.0;
+    t9_st8(slot_of(3), sA);
+
+    // ---------------- finalise plane (centre - 3): all six neighbouring planes have contributed
+    if (fin) {
+      double rsq = 0.0;
+      if (MAG) {
+        double pd[4];
+        { // {partial ds/dt, b} written in stage j-3
+          double t6[6];
+          t9_ld6(tmp + 8u * (uint32_t)((j + 1) & 3), t6);
+          pd[0] = t6[0]; pd[1] = t6[1]; pd[2] = t6[2]; pd[3] = t6[3];
+        }
+        const double *bq = pd + 1;
+        if (P.llorentzforce) { // jxbr = rho1*(jj x bb) (magnetic.f90:4870-4888, 5531)
+          rr[0] += rho1q * (jq[1] * bq[2] - jq[2] * bq[1]);
+          rr[1] += rho1q * (jq[2] * bq[0] - jq[0] * bq[2]);
+          rr[2] += rho1q * (jq[0] * bq[1] - jq[1] * bq[0]);
+        }
+        rsq = pd[0] + hTq * (jq[0] * jq[0] + jq[1] * jq[1] + jq[2] * jq[2]); // Ohmic heating (magnetic.f90:6138-6144)
+      }
+      double force[3] = {0., 0., 0.};
+      if (a.frc.on) { // forcing.f90:2170-2345
+        const double re = fxy_r * fzv.x - fxy_i * fzv.y, im = fxy_r * fzv.y + fxy_i * fzv.x;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) force[i] = a.frc.fda[i] * (a.frc.coef1[i] * re - a.frc.coef2[i] * im);
+      }
+      if (active) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) rk(rr[i], dfv[i], fq[i], (S::IUX + i) * sv - NG * sz, force[i]);
+        if (SDEL) rk(rsq, dfv[S::ISS], fq[3], S::ISS * sv - NG * sz, 0.0);
+      }
+    }
+
+    pdf += sz;
+    pfo += sz;
+    if (++slot == V9_NSLOT) { slot = 0; par ^= 1; }
+    if (j + 1 < nst && tid >= 32) named_bar_arrive(1 + (j & 7), V2_THREADS);
+  }
+  t9_wait_st();
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (tid < 32) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(*tm_slot) : "memory");
+}
+
+} // namespace pcb200

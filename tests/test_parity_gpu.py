@@ -33,12 +33,15 @@ def _cfg(name, **over):
     return c
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8])
+VARIANTS = [1, 4, 5, 9]
+
+
+@pytest.mark.parametrize("variant", VARIANTS)
 @pytest.mark.parametrize("name", sorted(CASES))
 def test_one_substep(oracle_mod, name, variant):
-    """variant 1 = global-load kernel, 2 = TMA/shared-memory z-marching kernel (needs even mx), 3 = 2 with the physics
-    split over hydro/magnetic warp roles, 4 = lead/trail z-mixed derivatives, 5 = isotropic-spacing specialisation
-    (default), 6/7 = 5 with z histories in tensor memory, 8 = 7 with 12 warps on a 32x12 tile"""
+    """variant 1 = global-load kernel (fallback for odd mx, cross-check), 4 = TMA/shared-memory z-marching kernel with
+    lead/trail z-mixed derivatives (anisotropic grids), 5 = its isotropic-spacing specialisation (round-1 default),
+    9 = all-trail z-mixed derivatives with delayed finalisation, z histories and accumulators in tensor memory (default)"""
     cfg = _cfg(name)
     if variant >= 2 and cfg["nx"] % 2:
         pytest.skip("TMA variant needs 16-byte row strides (even mx); odd grids use variant 1")
@@ -47,14 +50,14 @@ def test_one_substep(oracle_mod, name, variant):
     assert err.max() <= TOL_SUBSTEP, (name, variant, err)
 
 
-@pytest.mark.parametrize("variant", [2, 3, 4, 5, 6, 7, 8])
-@pytest.mark.parametrize("shape", [(32, 8, 4), (64, 16, 40), (70, 9, 5), (6, 6, 6), (34, 10, 17)])
+@pytest.mark.parametrize("variant", [4, 5, 9])
+@pytest.mark.parametrize("shape", [(32, 8, 4), (64, 16, 40), (70, 9, 5), (6, 6, 6), (34, 10, 17), (40, 24, 3), (32, 8, 100)])
 def test_tma_variants_tile_edges(oracle_mod, shape, variant):
-    """grids that are not multiples of the 32x8 (variant 8: 32x12) tile, shorter than one tile, and z-chunk remainders"""
+    """grids that are not multiples of the 32x8 tile, shorter than one tile, the minimum nz = 3, and z-chunk remainders"""
     nx, ny, nz = shape
     cfg = pcfg.make_config(nx, True, True, ny=ny, nz=nz, nu=5e-3, eta=4e-3, chi=3e-3, cdt=0.4, cdtv=0.3)
     cfg.update(dx=0.2, dy=0.21, dz=0.19)
-    if variant >= 5:  # variants 5/6 are the isotropic-spacing specialisation (anisotropic grids fall back to 4)
+    if variant >= 5:  # variants 5 and 9 are isotropic-spacing specialisations (anisotropic grids fall back to 4)
         cfg.update(dx=0.2, dy=0.2, dz=0.2)
     fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 0, dt=0.01, substeps_only=3, kernel_variant=variant)
     assert pu.rel_linf(fg, fc).max() <= 5e-12, (shape, variant)
