@@ -71,6 +71,10 @@ typedef struct pcb200_config {
 
 /* must be called before initialize_gpu_c; copies *cfg */
 void pcb200_configure(const pcb200_config *cfg);
+/* RELOAD: new physics parameters while initialized (grid, decomposition and variable slots must be unchanged;
+   device and kernel_variant are kept); follow with reload_gpu_config_c.  Before initialize_gpu_c it equals
+   pcb200_configure. */
+void pcb200_reconfigure(const pcb200_config *cfg);
 int pcb200_sizeof_config(void);
 
 /* Timestep exchange with the host driver.  The Fortran module calls
@@ -137,6 +141,9 @@ void pcb200_synchronize(void);
 void pcb200_init_synthetic(const int *seed);
 /* number of kernels this library has launched so far (bench.py: gpu_launches) */
 long long pcb200_launch_count(void);
+/* number of blocking host synchronisations (cudaStream/Event/DeviceSynchronize) the library has issued so far: a
+   fixed-dt step without diagnostics must not add any (tests/test_parity_gpu.py) */
+long long pcb200_host_sync_count(void);
 /* device time in ms spent in the fused rhs+rk kernel since the last reset, and its launch count */
 void pcb200_kernel_timing(double *ms, long long *launches, const int *reset);
 void pcb200_enable_kernel_timing(const int *on);

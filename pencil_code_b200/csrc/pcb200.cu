@@ -35,11 +35,15 @@ namespace pcb200 {
   std::fflush(stderr);
   std::abort();
 }
+static long long g_host_syncs = 0; // blocking host synchronisations issued by the library (pcb200_host_sync_count)
 #define CK(call)                                                                                         \
   do {                                                                                                   \
     cudaError_t e_ = (call);                                                                             \
     if (e_ != cudaSuccess) die("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
   } while (0)
+#define SYNC_STREAM(st) do { ++g_host_syncs; CK(cudaStreamSynchronize st); } while (0)
+#define SYNC_EVENT(ev) do { ++g_host_syncs; CK(cudaEventSynchronize ev); } while (0)
+#define SYNC_DEVICE() do { ++g_host_syncs; CK(cudaDeviceSynchronize()); } while (0)
 
 // ---------------------------------------------------------------------------
 // Kernel 1 (variant 1): fused RHS + 2N-RK3 update, one cell per thread, taps through L1/L2.
@@ -421,6 +425,7 @@ struct State {
   size_t ybuf_doubles = 0;
   // dt
   double dt_host = 0.0;
+  bool dt_on_device = false; // dt_dev holds dt_host (fixed-dt mode)
   int ldt = 0;
   double *dt_dev = nullptr, *dt1_dev = nullptr;
   double *pinned = nullptr; // small pinned scratch (32 doubles)
@@ -434,7 +439,6 @@ struct State {
   int lforce = 0;
   double coef1[3], coef2[3], fda[3], kk[3], phase = 0, fact = 0, k1_ff = 1;
   double2 *fx_dev = nullptr, *fy_dev = nullptr, *fz_dev = nullptr;
-  double2 *ftab_host = nullptr;
   // nccl
   ncclComm_t comm = nullptr;
   int rank = 0, nranks = 1;
@@ -878,7 +882,7 @@ static void compute_diagnostics(cudaStream_t st) {
     NCK(nccl.GroupEnd());
   }
   CK(cudaMemcpyAsync(S.pinned + 8, S.diag_dev, sizeof(double) * (DS_NSUM + DM_NMAX), cudaMemcpyDeviceToHost, st));
-  CK(cudaStreamSynchronize(st));
+  SYNC_STREAM((st));
   const double *s = S.pinned + 8, *m = S.pinned + 8 + DS_NSUM;
   const double nw = (double)S.cfg.nx * S.cfg.ny * S.cfg.nz * S.cfg.nprocx * S.cfg.nprocy * S.cfg.nprocz; // nwgrid
   double *r = S.reduced;
@@ -901,32 +905,35 @@ static void compute_diagnostics(cudaStream_t st) {
   S.diag_valid = true;
 }
 
+// fxyz_coefs_hel forcing.f90:2003-2064: fx=exp(i(kx*k1_ff*x+phase))*fact, fy=exp(i ky k1_ff y), fz likewise.
+// Built on the device from scalars passed by value: no host staging buffer, so steps can be queued back to back
+// without a host synchronisation (the tables of step n+1 are written in stream order after step n's kernels).
+__global__ void forcing_tables_kernel(double2 *tab, int mx, int my, int mz, double kx, double ky, double kz, double phase,
+                                      double fact, double x0, double y0, double z0, double dx, double dy, double dz) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= mx + my + mz) return;
+  double arg, amp = 1.0;
+  if (i < mx) { arg = kx * (x0 + (i - NG) * dx) + phase; amp = fact; }
+  else if (i < mx + my) arg = ky * (y0 + (i - mx - NG) * dy);
+  else arg = kz * (z0 + (i - mx - my - NG) * dz);
+  double sn, cs;
+  sincos(arg, &sn, &cs);
+  tab[i] = make_double2(cs * amp, sn * amp);
+}
 static void upload_forcing_tables(cudaStream_t st) {
-  // fxyz_coefs_hel forcing.f90:2003-2064: fx=exp(i(kx*k1_ff*x+phase))*fact, fy=exp(i ky k1_ff y), fz likewise
   const Pars &P = S.P;
-  double2 *hx = S.ftab_host, *hy = hx + P.mx, *hz = hy + P.my;
-  for (int i = 0; i < P.mx; ++i) {
-    const double x = S.cfg.x0 + (i - NG) * S.cfg.dx;
-    const double arg = S.kk[0] * S.k1_ff * x + S.phase;
-    hx[i] = make_double2(std::cos(arg) * S.fact, std::sin(arg) * S.fact);
-  }
-  for (int i = 0; i < P.my; ++i) {
-    const double y = S.cfg.y0 + (i - NG) * S.cfg.dy;
-    const double arg = S.kk[1] * S.k1_ff * y;
-    hy[i] = make_double2(std::cos(arg), std::sin(arg));
-  }
-  for (int i = 0; i < P.mz; ++i) {
-    const double z = S.cfg.z0 + (i - NG) * S.cfg.dz;
-    const double arg = S.kk[2] * S.k1_ff * z;
-    hz[i] = make_double2(std::cos(arg), std::sin(arg));
-  }
-  CK(cudaMemcpyAsync(S.fx_dev, hx, sizeof(double2) * (P.mx + P.my + P.mz), cudaMemcpyHostToDevice, st));
+  const int n = P.mx + P.my + P.mz;
+  forcing_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(S.fx_dev, P.mx, P.my, P.mz, S.kk[0] * S.k1_ff, S.kk[1] * S.k1_ff,
+                                                         S.kk[2] * S.k1_ff, S.phase, S.fact, S.cfg.x0, S.cfg.y0, S.cfg.z0,
+                                                         S.cfg.dx, S.cfg.dy, S.cfg.dz);
+  CK(cudaGetLastError());
+  S.launches++;
 }
 
 static void drain_timing() {
   for (auto &p : S.ev_pending) {
     float ms = 0.f;
-    CK(cudaEventSynchronize(p.second));
+    SYNC_EVENT((p.second));
     CK(cudaEventElapsedTime(&ms, p.first, p.second));
     S.kernel_ms += ms;
     S.ev_pool.push_back(p.first);
@@ -953,25 +960,48 @@ extern "C" void pcb200_configure(const pcb200_config *cfg) {
   S.configured = true;
 }
 
+// RELOAD (gpu_b200.f90 reload_GPU_config): new physics parameters while initialized.  Sizes, decomposition, variable
+// slots, grid spacing and origin must be unchanged; device and kernel variant are kept.  reload_gpu_config_c then
+// rebuilds the device constants from the new values.
+extern "C" void pcb200_reconfigure(const pcb200_config *cfg) {
+  if (!S.initialized) { pcb200_configure(cfg); return; }
+  const pcb200_config &o = S.cfg;
+  if (cfg->nx != o.nx || cfg->ny != o.ny || cfg->nz != o.nz || cfg->nprocx != o.nprocx || cfg->nprocy != o.nprocy ||
+      cfg->nprocz != o.nprocz || cfg->ipx != o.ipx || cfg->ipy != o.ipy || cfg->ipz != o.ipz || cfg->nvar != o.nvar ||
+      cfg->iux != o.iux || cfg->ilnrho != o.ilnrho || cfg->iss != o.iss || cfg->iax != o.iax || cfg->dx != o.dx ||
+      cfg->dy != o.dy || cfg->dz != o.dz || cfg->x0 != o.x0 || cfg->y0 != o.y0 || cfg->z0 != o.z0)
+    die("pcb200_reconfigure: grid, decomposition and variable slots cannot change while initialized");
+  const int dev = o.device, kv = o.kernel_variant;
+  S.cfg = *cfg;
+  S.cfg.device = dev;
+  S.cfg.kernel_variant = kv;
+}
+
+__global__ void set_scalar_kernel(double *dst, double v) { *dst = v; }
+
+// Fixed-dt mode: the device copy of dt is rewritten only when the value changes, by a one-thread kernel that takes
+// it by value -- no staging buffer, no host synchronisation between steps.
 extern "C" void pcb200_set_dt(const double *dt, const int *ldt) {
+  const bool changed = !S.dt_on_device || *dt != S.dt_host || (*ldt != 0) != (S.ldt != 0);
   S.dt_host = *dt;
   S.ldt = *ldt;
-  if (S.initialized && !S.ldt) {
-    S.pinned[0] = S.dt_host;
-    CK(cudaMemcpyAsync(S.dt_dev, S.pinned, sizeof(double), cudaMemcpyHostToDevice, S.stream));
-    CK(cudaStreamSynchronize(S.stream)); // pinned[0] may be rewritten by the next call
+  if (S.ldt) S.dt_on_device = false; // compute_dt() owns dt_dev in Courant mode
+  if (S.initialized && !S.ldt && changed) {
+    set_scalar_kernel<<<1, 1, 0, S.stream>>>(S.dt_dev, S.dt_host);
+    CK(cudaGetLastError());
+    S.dt_on_device = true;
   }
 }
 extern "C" void pcb200_get_dt1_max(double *dt1_max) {
   need_init("pcb200_get_dt1_max");
   CK(cudaMemcpyAsync(S.pinned + 1, S.dt1_dev, sizeof(double), cudaMemcpyDeviceToHost, S.stream));
-  CK(cudaStreamSynchronize(S.stream));
+  SYNC_STREAM((S.stream));
   *dt1_max = S.pinned[1];
 }
 extern "C" void pcb200_get_dt(double *dt) {
   need_init("pcb200_get_dt");
   CK(cudaMemcpyAsync(S.pinned + 2, S.dt_dev, sizeof(double), cudaMemcpyDeviceToHost, S.stream));
-  CK(cudaStreamSynchronize(S.stream));
+  SYNC_STREAM((S.stream));
   *dt = S.pinned[2];
   S.dt_host = *dt;
 }
@@ -1030,7 +1060,7 @@ extern "C" void pcb200_p2p_export(unsigned char *blob) {
     CK(cudaMalloc(&S.flags, 2 * sizeof(unsigned long long)));
     CK(cudaMemset(S.flags, 0, 2 * sizeof(unsigned long long)));
     CK(cudaMalloc(&S.seq_slots, 16 * sizeof(unsigned long long)));
-    CK(cudaDeviceSynchronize());
+    SYNC_DEVICE();
   }
   cudaIpcMemHandle_t h[3];
   CK(cudaIpcGetMemHandle(&h[0], S.f[0]));
@@ -1072,12 +1102,12 @@ extern "C" void pcb200_p2p_enable(void) {
   if (S.cfg.nprocz < 2) return;
   if (!S.peer_f[0][0] || !S.peer_f[1][0]) die("pcb200_p2p_enable: not connected");
   wait_halo(S.stream); // an exchange started on the NCCL path finishes there
-  CK(cudaStreamSynchronize(S.stream));
+  SYNC_STREAM((S.stream));
   S.p2p = true;
 }
 
 extern "C" void pcb200_set_stream(void *cuda_stream) {
-  if (S.initialized) CK(cudaStreamSynchronize(S.stream));
+  if (S.initialized) SYNC_STREAM((S.stream));
   if (S.own_stream && S.stream) { CK(cudaStreamDestroy(S.stream)); S.own_stream = false; }
   if (cuda_stream) S.stream = (cudaStream_t)cuda_stream;
   else { CK(cudaStreamCreateWithFlags(&S.stream, cudaStreamNonBlocking)); S.own_stream = true; }
@@ -1085,11 +1115,12 @@ extern "C" void pcb200_set_stream(void *cuda_stream) {
 
 extern "C" void pcb200_synchronize(void) {
   need_init("pcb200_synchronize");
-  CK(cudaStreamSynchronize(S.stream));
-  CK(cudaStreamSynchronize(S.comm_stream));
+  SYNC_STREAM((S.stream));
+  SYNC_STREAM((S.comm_stream));
 }
 
 extern "C" long long pcb200_launch_count(void) { return S.launches; }
+extern "C" long long pcb200_host_sync_count(void) { return g_host_syncs; }
 
 extern "C" void pcb200_enable_kernel_timing(const int *on) { S.timing = (*on != 0); }
 extern "C" void pcb200_kernel_timing(double *ms, long long *launches, const int *reset) {
@@ -1203,11 +1234,11 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   CK(cudaMalloc(&S.fx_dev, sizeof(double2) * (P.mx + P.my + P.mz)));
   S.fy_dev = S.fx_dev + P.mx;
   S.fz_dev = S.fy_dev + P.my;
-  CK(cudaMallocHost(&S.ftab_host, sizeof(double2) * (P.mx + P.my + P.mz)));
   CK(cudaMemcpyToSymbolAsync(cP, &S.P, sizeof(Pars), 0, cudaMemcpyHostToDevice, S.stream));
   S.pinned[0] = S.dt_host;
   CK(cudaMemcpyAsync(S.dt_dev, S.pinned, sizeof(double), cudaMemcpyHostToDevice, S.stream));
-  CK(cudaStreamSynchronize(S.stream));
+  SYNC_STREAM((S.stream));
+  S.dt_on_device = !S.ldt;
   S.initialized = true;
 }
 FTN_ALIAS(initialize_gpu_c)
@@ -1217,7 +1248,7 @@ extern "C" void finalize_gpu_c(void) {
   if (S.p2p) { // both neighbours' last puts must have landed before the ghost planes they target are freed
     for (int d = 0; d < 2; ++d) drv_wait64((CUstream)S.stream, (CUdeviceptr)(S.flags + d), (cuuint64_t)S.seq, CU_STREAM_WAIT_VALUE_GEQ);
   }
-  CK(cudaDeviceSynchronize());
+  SYNC_DEVICE();
   drain_timing();
   for (cudaEvent_t e : S.ev_pool) cudaEventDestroy(e);
   S.ev_pool.clear();
@@ -1230,7 +1261,7 @@ extern "C" void finalize_gpu_c(void) {
   cudaFree(S.f[0]); cudaFree(S.f[1]); cudaFree(S.df);
   if (S.ybuf) cudaFree(S.ybuf);
   cudaFree(S.dt_dev); cudaFree(S.dt1_dev); cudaFree(S.partial); cudaFree(S.diag_dev); cudaFree(S.fx_dev);
-  cudaFreeHost(S.pinned); cudaFreeHost(S.ftab_host);
+  cudaFreeHost(S.pinned);
   cudaEventDestroy(S.ev_ready); cudaEventDestroy(S.ev_halo);
   cudaStreamDestroy(S.comm_stream);
   if (S.own_stream) cudaStreamDestroy(S.stream);
@@ -1245,9 +1276,20 @@ extern "C" void load_farray_c(void) {
   need_init("load_farray_c");
   wait_halo(S.stream);
   if (!S.host_f) die("load_farray_c: no host f-array was retained by initialize_gpu_c");
-  CK(cudaMemcpyAsync(S.f[S.cur], S.host_f, S.nreal * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  if (S.cfg.nprocz > 1 || S.loopback) {
+    // z is decomposed: the exchange below rewrites the z-ghost planes, and with the peer-put halo a neighbour whose
+    // upload finishes earlier may already have written them -- a whole-array copy would overwrite its planes with
+    // stale host data after the arrival flag was raised.  Copy the interior planes only (contiguous per variable).
+    const size_t planes = (size_t)S.P.nz * S.P.sz;
+    for (int k = 0; k < S.P.nvar; ++k) {
+      const size_t off = (size_t)k * S.P.sv + (size_t)NG * S.P.sz;
+      CK(cudaMemcpyAsync(S.f[S.cur] + off, S.host_f + off, planes * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+    }
+  } else {
+    CK(cudaMemcpyAsync(S.f[S.cur], S.host_f, S.nreal * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+  }
   update_ghosts(S.f[S.cur], S.stream);
-  CK(cudaStreamSynchronize(S.stream));
+  SYNC_STREAM((S.stream));
 }
 FTN_ALIAS(load_farray_c)
 
@@ -1255,7 +1297,7 @@ extern "C" void copy_farray_c(double *f) {
   need_init("copy_farray_c");
   wait_halo(S.stream);
   CK(cudaMemcpyAsync(f, S.f[S.cur], S.nreal * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
-  CK(cudaStreamSynchronize(S.stream));
+  SYNC_STREAM((S.stream));
 }
 FTN_ALIAS(copy_farray_c)
 
@@ -1271,7 +1313,7 @@ extern "C" void pcb200_copy_farray_async(double *f) {
     CK(cudaEventCreateWithFlags(&S.ev_d2h, cudaEventDisableTiming));
     CK(cudaMalloc(&S.snap, S.nreal * sizeof(double)));
   }
-  if (S.d2h_pending) { CK(cudaEventSynchronize(S.ev_d2h)); S.d2h_pending = false; }
+  if (S.d2h_pending) { SYNC_EVENT((S.ev_d2h)); S.d2h_pending = false; }
   wait_halo(S.stream);
   CK(cudaMemcpyAsync(S.snap, S.f[S.cur], S.nreal * sizeof(double), cudaMemcpyDeviceToDevice, S.stream));
   CK(cudaEventRecord(S.ev_snap, S.stream));
@@ -1282,7 +1324,7 @@ extern "C" void pcb200_copy_farray_async(double *f) {
 }
 extern "C" void pcb200_copy_farray_wait(void) {
   need_init("pcb200_copy_farray_wait");
-  if (S.d2h_pending) { CK(cudaEventSynchronize(S.ev_d2h)); S.d2h_pending = false; }
+  if (S.d2h_pending) { SYNC_EVENT((S.ev_d2h)); S.d2h_pending = false; }
 }
 
 extern "C" void get_farray_ptr_gpu_c(double **p_in, double **p_out) {
@@ -1305,7 +1347,7 @@ FTN_ALIAS(radtransfer_gpu_c)
 extern "C" void reload_gpu_config_c(void) {
   need_init("reload_gpu_config_c");
   derive_pars();
-  CK(cudaStreamSynchronize(S.stream));
+  SYNC_STREAM((S.stream));
   CK(cudaMemcpyToSymbol(cP, &S.P, sizeof(Pars)));
 }
 FTN_ALIAS(reload_gpu_config_c)
@@ -1369,7 +1411,7 @@ extern "C" void rhs_gpu_c(int *isubstep, double *t) {
     pcb200_get_dt(&d);
     S.reduced[PCB200_RED_DT] = d;
     CK(cudaMemcpyAsync(S.pinned + 1, S.dt1_dev, sizeof(double), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    SYNC_STREAM((st));
     S.reduced[PCB200_RED_DT1MAX] = S.pinned[1];
   } else if (it == 1) {
     S.reduced[PCB200_RED_DT] = S.dt_host;
@@ -1387,12 +1429,12 @@ extern "C" void test_bcs_c(void) { need_init("test_bcs_c"); }
 FTN_ALIAS(test_bcs_c)
 
 // updateInConfig* (gpu_astaroth.cc:2179-2241): run-time parameter pushes by name
-static const char *scal_names[] = {"nu", "eta", "chi", "nu_hyper3", "diffrho_hyper3", "cs20", "cdt", "cdtv", "cdtv3", nullptr};
+static const char *scal_names[] = {"nu", "eta", "chi", "nu_hyper3", "diffrho_hyper3", "cs20", "cdt", "cdtv", "cdtv3", "cdtv2", nullptr};
 static double *scal_ptr(int i) {
   switch (i) {
   case 0: return &S.cfg.nu; case 1: return &S.cfg.eta; case 2: return &S.cfg.chi; case 3: return &S.cfg.nu_hyper3;
   case 4: return &S.cfg.diffrho_hyper3; case 5: return &S.cfg.cs20; case 6: return &S.cfg.cdt; case 7: return &S.cfg.cdtv;
-  case 8: return &S.cfg.cdtv3; default: return nullptr;
+  case 8: return &S.cfg.cdtv3; case 9: return &S.cfg.cdtv2; default: return nullptr;
   }
 }
 extern "C" void update_on_gpu_scal_by_ind_c(int *index, double *value) {

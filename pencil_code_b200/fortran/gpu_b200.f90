@@ -68,6 +68,17 @@ module GPU
       import :: c_double
       real(c_double), intent(out) :: dt
     endsubroutine
+    subroutine pcb200_hand_dt1_to_set_dt_c() bind(C,name="pcb200_hand_dt1_to_set_dt_c")
+    endsubroutine
+    function pcb200_forcing_supported_c(nx_,my_,mz_) bind(C,name="pcb200_forcing_supported_c") result(ok)
+      import :: c_int
+      integer(c_int), intent(in) :: nx_, my_, mz_
+      integer(c_int) :: ok
+    endfunction
+    subroutine pcb200_reconfigure(cfg) bind(C,name="pcb200_reconfigure")
+      import :: pcb200_config
+      type(pcb200_config), intent(in) :: cfg
+    endsubroutine
     subroutine pcb200_nccl_get_unique_id(id) bind(C,name="pcb200_nccl_get_unique_id")
       import :: c_char
       character(kind=c_char), dimension(128), intent(out) :: id
@@ -167,7 +178,7 @@ module GPU
   logical :: ltest_bcs=.false.     !PAR-DOC: accepted for namelist compatibility with gpu_astaroth
   logical :: ltest_rhs=.false.     !PAR-DOC: run test_rhs_gpu (equ.f90:1974-2143) at step it_test_rhs
   integer :: it_test_rhs=1
-  integer :: kernel_variant=0      !PAR-DOC: 0=auto (5 on isotropic grids, else 4; 1 for odd mx), 1=global-load kernel, 2-8=TMA z-marching kernels (include/pcb200.h)
+  integer :: kernel_variant=0      !PAR-DOC: 0=auto (9 on isotropic grids, else 4; 1 for odd mx), 1=global-load kernel, 4/5/9=TMA z-marching kernels (include/pcb200.h)
   integer :: gpu_device=-1         !PAR-DOC: CUDA device; -1 = local rank modulo device count
 
   logical :: lp2p_halo=.true.      !PAR-DOC: z halos as peer-memory puts over NVLink (else NCCL send/recv)
@@ -227,6 +238,18 @@ contains
       if (.not.all(lperi))        call fatal_error('initialize_GPU','gpu_b200: periodic boundaries only')
       if (nprocx/=1)              call fatal_error('initialize_GPU','gpu_b200: nprocx must be 1')
       if (itorder/=3)             call fatal_error('initialize_GPU','gpu_b200: itorder=3 only')
+      if (ddt>0.)                 call fatal_error('initialize_GPU','gpu_b200: time-step growth limiter (ddt>0) not supported')
+      if (loutput_varn_at_exact_tsnap) &
+                                  call fatal_error('initialize_GPU','gpu_b200: loutput_varn_at_exact_tsnap (shift_dt) not supported')
+!
+!  Forcing: run.f90:575 skips addforce when lgpu, so anything but the delta-correlated helical forcing with its
+!  default options (no profiles, no second force, no continuous forcing, no momentum forcing) would be dropped
+!  silently -> refuse it (the switches are private to Forcing: read through its pushpars2c table by the C shim).
+!
+      if (lforcing) then
+        if (pcb200_forcing_supported_c(nx,my,mz)==0) call fatal_error('initialize_GPU', &
+            "gpu_b200: only iforce='helical' without profiles, iforce2, lforcing_cont, lmomentum_ff, iforcing_zsym")
+      endif
 !
       cfg%nx=nx; cfg%ny=ny; cfg%nz=nz
       cfg%nprocx=nprocx; cfg%nprocy=nprocy; cfg%nprocz=nprocz
@@ -366,8 +389,14 @@ contains
       if (isubstep==itorder .and. lforcing) call pcb200_push_forcing_c   ! astaroth/forcing.h:1-36
       call rhs_gpu_c(isub,t)
       if (isubstep==1 .and. ldt) then
-        call pcb200_get_dt(dt_c)       ! already max-reduced over all GPUs (sub.f90:4241-4245 skips MPI when lgpu)
-        dt=dt_c
+!
+!  The device has reduced dt1 over all cells and all GPUs and used dt=1/dt1 in this substep.  Pencil's own
+!  bookkeeping goes through set_dt (sub.f90:4223-4254, as gpu_astaroth.cc:1617-1634 does): with lgpu it skips the
+!  MPI reduction and forms dt=1./dt1 -- the same double-precision division as on the device, so both sides
+!  integrate with bit-identical dt.  The growth limiter (ddt>0) and shift_dt would change dt on the host only and
+!  are refused in initialize_GPU.
+!
+        call pcb200_hand_dt1_to_set_dt_c   ! C shim: pcb200_get_dt1_max -> Sub::set_dt (module GPU cannot use Sub)
       endif
 
     endsubroutine rhs_GPU
@@ -436,11 +465,28 @@ contains
     endfunction get_ptr_GPU_training
 !***********************************************************************
     subroutine copy_farray_from_GPU(f,nowait_)
+!
+!  Same protocol as gpu_astaroth.f90:390-412: with the OpenMP helper thread (MULTITHREADING=openmp) f may still
+!  be read by perform_diagnostics, so the copy waits until the helper has finished (lhelper_perf=F) and is
+!  done only once per diagnostic step (lfarray_copied); nowait_=T copies unconditionally.
+!
+!$    use General, only: signal_wait
 
       real, dimension (mx,my,mz,mfarray), intent(OUT) :: f
       logical, optional :: nowait_
 
-      call copy_farray_c(f)        ! synchronous; all mvar slots incl. valid ghost zones
+      if (loptest(nowait_)) then
+        call copy_farray_c(f)      ! synchronous; all mvar slots incl. valid ghost zones
+        return
+      endif
+!
+!$    if (lfarray_copied) return
+!
+!  Have to wait: the helper thread's diagnostics must not see a half-overwritten f.
+!
+!$    call signal_wait(lhelper_perf, .false.)
+      call copy_farray_c(f)
+!$    lfarray_copied = .true.
 
     endsubroutine copy_farray_from_GPU
 !***********************************************************************
@@ -454,8 +500,13 @@ contains
     endsubroutine load_farray_to_GPU
 !***********************************************************************
     subroutine reload_GPU_config
-
+!
+!  RELOAD: re-read the physics parameters from the modules and hand them to the library (sizes, decomposition and
+!  variable slots must be unchanged: pcb200_reconfigure refuses anything else), then rebuild the device constants.
+!
       call pcb200_fill_physics_pars_c(cfg)
+      cfg%cdt=cdt; cfg%cdtv=cdtv; cfg%cdtv2=cdtv2; cfg%cdtv3=cdtv3; cfg%dtmax=dtmax
+      call pcb200_reconfigure(cfg)
       call reload_gpu_config_c
 
     endsubroutine reload_GPU_config

@@ -39,6 +39,7 @@ extern void MODPROC(energy, pushpars2c)(FINT8 *);
 extern void MODPROC(forcing, forcing_pars_hel)(REAL *coef1, REAL *coef2, REAL *coef3, REAL *fda, REAL *kk,
                                                REAL *phase, REAL *fact);
 extern void MODPROC(forcing, pushpars2c)(FINT8 *);
+extern void MODPROC(sub, set_dt)(REAL *dt1_); /* sub.f90:4223-4254; the name scripts/sub2c builds for the Astaroth glue */
 
 #define PD(tab, i) (*(double *)(tab)[(i)-1])
 #define PI_(tab, i) (*(int *)(tab)[(i)-1])
@@ -91,4 +92,40 @@ void pcb200_push_forcing_c(void)
   MODPROC(forcing, pushpars2c)(p);
   k1_ff = PD(p, 1); /* forcing.f90:6620 */
   pcb200_set_forcing_hel(&on, coef1, coef2, fda, kk, &phase, &fact, &k1_ff);
+}
+
+/* Courant step: the device has reduced dt1 = max over all cells and GPUs inside substep 1.  Pencil's own dt goes
+   through Sub::set_dt exactly as in astaroth/gpu_astaroth.cc:1617-1634 (lgpu: no MPI reduction, dt=1./dt1). */
+void pcb200_hand_dt1_to_set_dt_c(void)
+{
+  double dt1;
+  REAL dt1_;
+  pcb200_get_dt1_max(&dt1);
+  dt1_ = (REAL)dt1;
+  MODPROC(sub, set_dt)(&dt1_);
+}
+
+/* 1 if the forcing configured in forcing_run_pars is the one this module implements on the device: iforce='helical'
+   (lforce_helical(1), forcing.f90:6609-6612), no second forcing function, no continuous forcing, no momentum
+   forcing, no z symmetrisation.  Table indices: forcing.f90:6618-6706 (iforcing_zsym 3, n_forcing_cont 10,
+   lmomentum_ff 21, lforce_helical 82, lsecond_force 83).  iforce_profile is not pushed as a switch, only the profile
+   arrays are (4-9): iforce_profile='nothing' leaves all of them 1 (forcing.f90:373-379), which is what is checked. */
+int pcb200_forcing_supported_c(const int *nx, const int *my, const int *mz)
+{
+  static FINT8 p[NPAR_MAX];
+  int i, k;
+  const int len[6] = {*nx, *my, *mz, *nx, *my, *mz};
+  for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+  MODPROC(forcing, pushpars2c)(p);
+  if (!PI_(p, 82)) return 0;      /* lforce_helical(1) */
+  if (PI_(p, 83)) return 0;       /* lsecond_force */
+  if (PI_(p, 10) != 0) return 0;  /* n_forcing_cont */
+  if (PI_(p, 21)) return 0;       /* lmomentum_ff */
+  if (PI_(p, 3) != 0) return 0;   /* iforcing_zsym */
+  for (k = 0; k < 6; k++) {       /* profx_ampl, profy_ampl, profz_ampl, profx_hel, profy_hel, profz_hel */
+    const REAL *prof = (const REAL *)p[3 + k];
+    for (i = 0; i < len[k]; i++)
+      if (prof[i] != (REAL)1.) return 0;
+  }
+  return 1;
 }

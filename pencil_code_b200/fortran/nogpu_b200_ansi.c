@@ -14,6 +14,9 @@ static void not_in_start(const char *who)
   exit(EXIT_FAILURE);
 }
 void pcb200_configure(const pcb200_config *cfg) { (void)cfg; }
+void pcb200_reconfigure(const pcb200_config *cfg) { (void)cfg; }
+void pcb200_hand_dt1_to_set_dt_c(void) { not_in_start("pcb200_hand_dt1_to_set_dt_c"); }
+int pcb200_forcing_supported_c(const int *nx, const int *my, const int *mz) { (void)nx; (void)my; (void)mz; return 1; }
 int pcb200_sizeof_config(void) { return (int)sizeof(pcb200_config); }
 void pcb200_fill_physics_pars_c(pcb200_config *cfg) { (void)cfg; }
 void pcb200_push_forcing_c(void) {}

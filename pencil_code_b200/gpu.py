@@ -57,9 +57,9 @@ class DriverState(C.Structure):
 
 # every symbol include/pcb200.h declares (checked by tests/test_abi.py on CPU)
 ABI_SYMBOLS = (
-    "pcb200_configure", "pcb200_sizeof_config", "pcb200_set_dt", "pcb200_get_dt1_max", "pcb200_get_dt",
+    "pcb200_configure", "pcb200_reconfigure", "pcb200_sizeof_config", "pcb200_set_dt", "pcb200_get_dt1_max", "pcb200_get_dt",
     "pcb200_set_forcing_hel", "pcb200_forcing_coefs_hel", "pcb200_request_diagnostics", "pcb200_nccl_get_unique_id", "pcb200_nccl_init",
-    "pcb200_set_stream", "pcb200_synchronize", "pcb200_init_synthetic", "pcb200_launch_count",
+    "pcb200_set_stream", "pcb200_synchronize", "pcb200_init_synthetic", "pcb200_launch_count", "pcb200_host_sync_count",
     "pcb200_kernel_timing", "pcb200_enable_kernel_timing",
     "pcb200_p2p_blob_bytes", "pcb200_p2p_export", "pcb200_p2p_connect", "pcb200_p2p_enable",
     "pcb200_copy_farray_async", "pcb200_copy_farray_wait", "pcb200_write_snapshot", "pcb200_read_snapshot",
@@ -107,6 +107,7 @@ def load_library():
     L.pcb200_read_snapshot.restype = C.c_int
     L.pcb200_init_synthetic.argtypes = [ip]
     L.pcb200_launch_count.restype = C.c_longlong
+    L.pcb200_host_sync_count.restype = C.c_longlong
     L.pcb200_kernel_timing.argtypes = [dp, C.POINTER(C.c_longlong), ip]
     L.pcb200_enable_kernel_timing.argtypes = [ip]
     L.initialize_gpu_c.argtypes = [dp, ip, dp, ip, ip, ip, ip]
@@ -292,6 +293,9 @@ class GPU:
 
     def launch_count(self):
         return int(self.L.pcb200_launch_count())
+
+    def host_sync_count(self):
+        return int(self.L.pcb200_host_sync_count())
 
     def enable_kernel_timing(self, on=True):
         self.L.pcb200_enable_kernel_timing(C.byref(C.c_int(int(on))))

@@ -76,9 +76,11 @@ def test_start_stub_resolves_every_bound_name(tmp_path):
     stub = {l.split()[2] for l in nm.splitlines() if len(l.split()) == 3 and l.split()[1] == "T"}
     bound = set(re.findall(r'bind\(c,\s*name="([a-z0-9_]+)"\)', open(os.path.join(fdir, "gpu_b200.f90")).read().lower()))
     assert bound and bound <= stub, sorted(bound - stub)
-    shim = set(re.findall(r"^void (\w+)\(", open(os.path.join(fdir, "gpu_b200_ansi.c")).read(), re.M))
+    shim = set(re.findall(r"^(?:void|int) (\w+)\(", open(os.path.join(fdir, "gpu_b200_ansi.c")).read(), re.M))
     L = gpu.load_library()
     for name in bound:
         assert name in shim or hasattr(L, name), name
     patch = open(os.path.join(fdir, "Makefile.src.patch")).read()
     assert "gpu_b200_ansi.o" in patch and "nogpu_b200_ansi.o" in patch and "-lpcb200" in patch
+    # the diagnostics of a GPU run are computed by the OpenMP helper thread (Makefile.src:509-515 for gpu_astaroth)
+    assert "override MULTITHREADING=openmp" in patch

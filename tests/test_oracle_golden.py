@@ -118,6 +118,53 @@ def test_gputest_known_answer_row0(oracle_mod):
     assert "%.4f" % d["rhom"] == "3.4212"
 
 
+def _gputest_setup():
+    """samples/gputest as its CPU run was configured (cpu-test.out:98-272): 32^3, [-pi,pi]^3, ABC flow k=2 amplitude 1,
+    lnrho=1.23, ss=0, A=0, nu=1e-3, eta=1e-3, heat conduction 'nothing', viscous + Ohmic heating on, dt=1e-3 fixed."""
+    n = 32
+    cfg = pcfg.make_config(n, entropy=True, magnetic=True, nu=1e-3, eta=1e-3, chi=0.0, cdt=0.4, cdtv=0.3)
+    f = np.zeros(synthetic.farray_shape(cfg))
+    i = np.arange(n)
+    x = (cfg["x0"] + i * cfg["dx"])[None, None, :]
+    y = (cfg["y0"] + i * cfg["dy"])[None, :, None]
+    z = (cfg["z0"] + i * cfg["dz"])[:, None, None]
+    I = (slice(3, -3),) * 3
+    f[0][I] = np.sin(2 * z) + np.cos(2 * y) + 0 * x  # hydro.f90:2214-2221 (inituu='ABC')
+    f[1][I] = np.sin(2 * x) + np.cos(2 * z) + 0 * y
+    f[2][I] = np.sin(2 * y) + np.cos(2 * x) + 0 * z
+    f[3][I] = 1.23
+    return cfg, f
+
+
+def gputest_rows():
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "gputest_cpu_rows.txt")
+    rows = [l.split() for l in open(path) if not l.startswith("#")]
+    assert len(rows) == 20
+    return rows
+
+
+def format_gputest_row(d):
+    """print.in formats: urms(f10.5) umax(f10.5) epsK(e10.3) rhom(f9.4); Fortran e10.3 prints 0.xxxE+yy only without
+    the 1p scale factor -- legend.f90 adds 1p, so the mantissa is d.ddd as in C's %.3E."""
+    return ["%.5f" % d["urms"], "%.5f" % d["umax"], "%.3E" % d["epsK"], "%.4f" % d["rhom"]]
+
+
+def test_gputest_20_rows_of_the_reference_cpu_binary(oracle_mod):
+    """All 20 time-series rows the reference's own CPU build printed for samples/gputest (cpu-test.out:275-294,
+    committed as tests/golden/gputest_cpu_rows.txt): 20 RK3 steps of hydro + continuity + entropy (viscous heating)
+    + induction, every printed digit of urms, umax, epsK, rhom."""
+    cfg, f = _gputest_setup()
+    o = oracle_mod.Oracle(cfg)
+    o.update_ghosts(f)
+    df = np.zeros_like(f)
+    t, dt = 0.0, 1e-3
+    for row in gputest_rows():
+        dt, t, d = o.time_step(f, df, False, dt, t, diag=True)
+        assert format_gputest_row(d) == row[2:6], (row, d)
+        assert "%.2E" % dt == row[1]
+
+
 def test_periodic_ghosts(oracle_mod):
     cfg = pcfg.make_config(8, True, True, ny=6, nz=5)
     o = oracle_mod.Oracle(cfg)

@@ -120,6 +120,29 @@ def test_helical_forcing_30_steps(oracle_mod):
     assert np.abs(pu.interior(fg)[:3] - pu.interior(fg0)[:3]).max() > 1e-4
 
 
+def test_helical_forcing_300_steps_64_and_no_host_sync(oracle_mod):
+    """300 forced steps at 64^3 against the oracle, and the fixed-dt time loop queues its steps without a single
+    blocking host synchronisation (dt is uploaded only when it changes, the forcing tables are built on the device)."""
+    from pencil_code_b200.gpu import GPU, HelicalForcing
+    cfg = pcfg.make_config(64, False, True, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3)
+    kv = pcfg.kvectors()
+    fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 300, dt=pcfg.fixed_dt(cfg), forcing=kv)
+    assert pu.rel_linf(fg, fc).max() <= TOL_100
+    f = synthetic.initial_condition(cfg)
+    g = GPU(cfg)
+    g.initialize_GPU(f)
+    try:
+        hf = HelicalForcing(kv)
+        dt, t = pcfg.fixed_dt(cfg), 0.0
+        _, t = g.time_step(f, dt, False, t, forcing=hf.draw(dt))  # first step uploads dt
+        n0 = g.host_sync_count()
+        for _ in range(20):
+            _, t = g.time_step(f, dt, False, t, forcing=hf.draw(dt))
+        assert g.host_sync_count() == n0
+    finally:
+        g.finalize_GPU()
+
+
 def test_hyper3_20_steps(oracle_mod):
     cfg = _cfg("hydro_hyper3")
     fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 20, dt=pcfg.fixed_dt(cfg))
@@ -296,3 +319,21 @@ def test_multi_gpu_decomposition_invariance():
                         "--master-addr", "127.0.0.1", "--master-port", "29533", script], capture_output=True, text=True,
                        timeout=600)
     assert r.returncode == 0 and "MULTI_GPU_CHECK PASS" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_gputest_20_rows_of_the_reference_cpu_binary_on_the_gpu():
+    """The reference's own known-answer run (samples/gputest/cpu-test.out:275-294, tests/golden/gputest_cpu_rows.txt)
+    through the C ABI: 20 RK3 steps, get_gpu_reduced_vars formatted with print.in's formats must reproduce every digit
+    the reference's CPU binary printed."""
+    from pencil_code_b200.gpu import GPU
+    from test_oracle_golden import _gputest_setup, format_gputest_row, gputest_rows
+    cfg, f = _gputest_setup()
+    g = GPU(cfg)
+    g.initialize_GPU(f)
+    t, dt = 0.0, 1e-3
+    try:
+        for row in gputest_rows():
+            dt, t = g.time_step(f, dt, False, t, diagnostics=True)
+            assert format_gputest_row(g.get_gpu_reduced_vars()) == row[2:6], row
+    finally:
+        g.finalize_GPU()
