@@ -85,50 +85,94 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def cpu_oracle_throughput(n, steps, nthreads=0):
-    """cell-substep-updates/s of the CPU restatement (-O3 -march=native, OpenMP over (m,n) pencils)
-    on an n^3 periodic sample of the same 8-variable physics."""
+def host_threads():
+    """threads this process may actually use (torchrun exports OMP_NUM_THREADS=1: the affinity mask is what counts)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+CPU_WINDOW_NZ = 64  # z-planes of the bounded CPU sample
+
+
+def cpu_oracle_throughput(args, steps, warmup=1):
+    """cell-substep-updates/s of the CPU restatement (-O3 -march=native, OpenMP over (m,n) pencils, all host threads)
+    on a bounded sample of the bench workload: the global grid's full x and y extent (same pencil length and
+    plane size as the real run) and a CPU_WINDOW_NZ-plane periodic window in z; one step = one RK3 step with the
+    workload's forcing.  Returns (value, seconds per step, threads, description)."""
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import numpy as np
     import pc_oracle
     from pencil_code_b200 import config as pcfg
     from pencil_code_b200 import synthetic
-    cfg = pcfg.config_mhd_entropy(n)
+    n = args.n
+    nzw = min(CPU_WINDOW_NZ, n)
+    cfg, wname = workload_config(args, n, 1, 0, 1, 0)
+    cfg = dict(cfg, nz=nzw)
+    nthreads = host_threads()
+    os.environ["OMP_NUM_THREADS"] = str(nthreads)
     outdir = tempfile.mkdtemp(prefix="pc_oracle_fast_")  # -march=native must be built on the box that runs it
     o = pc_oracle.Oracle(cfg, nthreads=nthreads, fast=True, outdir=outdir)
     f = synthetic.initial_condition(cfg)
     df = np.zeros_like(f)
     dt, t = pcfg.fixed_dt(cfg), 0.0
-    o.time_step(f, df, False, dt, t)  # warm-up (page faults, thread pool)
+    for _ in range(max(warmup, 1)):  # page faults, thread pool
+        dt, t, _ = o.time_step(f, df, False, dt, t)
     t0 = time.perf_counter()
     for _ in range(steps):
         dt, t, _ = o.time_step(f, df, False, dt, t)
     el = time.perf_counter() - t0
-    ncores = nthreads if nthreads > 0 else (os.cpu_count() or 1)
-    return n ** 3 * 3 * steps / el, el, ncores
+    desc = ("%d x %d x %d z-window (periodic) of the %d^3 grid, %d variables, same physics, %d RK3 steps in %.1f s on %d "
+            "threads; CPU restatement of the reference (oracle, g++ -O3 -march=native -fopenmp) -- the Fortran code "
+            "cannot be built here (no gfortran/MPI)" % (n, n, nzw, n, cfg["nvar"], steps, el, nthreads))
+    return n * n * nzw * 3 * steps / el, el / max(steps, 1), nthreads, desc
+
+
+def workload_config(args, n, npy, ipy, npz, ipz):
+    from pencil_code_b200 import config as pcfg
+    if args.workload == "iso_mhd":
+        cfg = pcfg.make_config(n, entropy=False, magnetic=True, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3,
+                               nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
+        wname = "isothermal forced MHD turbulence %d^3 (lnrho, uu, aa: 7 vars, FP64)" % n
+    elif args.workload == "hydro_hyper3":
+        cfg = pcfg.config_hydro_hyper3(n, nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
+        wname = "hydro-only forced turbulence %d^3 with 6th-order hyperdiffusion (4 vars, FP64)" % n
+    else:
+        cfg = pcfg.config_mhd_entropy(n, nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
+        wname = "periodic MHD with entropy %d^3 (8 vars, FP64)" % n
+    return cfg, wname
+
+
+def config_dict(args, world, wname, nvar, nbytes_f):
+    """the `config` object of the JSON line -- identical for the b200 arm and the reference arm"""
+    from pencil_code_b200 import decomp
+    npy, npz = decomp.choose_decomposition(world, args.decomp)
+    return {"workload": wname + ", helical forcing, fixed dt, 2N-RK3",
+            "decomposition": "1x%dx%d %s" % (npy, npz, "z-slabs" if npy == 1 else "yz-pencils"), "nvar": nvar,
+            "l2": "inputs larger than L2 (%.1f GB per f buffer per GPU)" % (nbytes_f / 1e9)}
 
 
 def run_reference(args, rank):
-    """--impl reference: the reference's CPU implementation of the path.  The Fortran code cannot be
-    compiled in this image (no gfortran/MPI), so this times the CPU oracle (restatement) with all host
-    threads on a bounded sample (256^3, same physics; one step = one RK3 step of the sample, ~1 s on 16 cores)
-    of the workload."""
+    """--impl reference: the reference's CPU implementation of the path on the box's host cores.  The Fortran code
+    cannot be compiled in this image (no gfortran/MPI), so this times the CPU oracle (restatement, kind "port") with
+    all host threads; every step is one RK3 step of a bounded sample of the workload (cpu_oracle_throughput)."""
     if rank != 0:
         return
-    n = 256
-    per_step = []
-    for _ in range(max(args.warmup, 0)):
-        pass  # warm-up is inside cpu_oracle_throughput
-    val, el, cores = cpu_oracle_throughput(n, max(args.steps, 1))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    val, s_per_step, cores, desc = cpu_oracle_throughput(args, max(args.steps, 1), max(args.warmup, 1))
+    n = args.n
+    cfg, wname = workload_config(args, n, 1, 0, 1, 0)
+    import numpy as np
+    from pencil_code_b200 import decomp
+    npy, npz = decomp.choose_decomposition(world, args.decomp)
+    nbytes_f = (n + 6) * (n // npy + 6) * (n // npz + 6) * cfg["nvar"] * 8
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": el / max(args.steps, 1) * 1e3, "higher_is_better": True,
+        "warmup": args.warmup, "ms_per_step": s_per_step * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "periodic MHD with entropy %d^3 (8 vars, FP64), fixed dt" % args.n,
-                   "sample": "%d^3 periodic box, same physics, per step" % n},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": "%d^3 x %d RK3 steps, CPU restatement (oracle, g++ -O3 -march=native -fopenmp); "
-                                   "the Fortran reference cannot be built here (no gfortran/MPI)" % (n, args.steps)},
+        "config": config_dict(args, world, wname, cfg["nvar"], nbytes_f),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -187,16 +231,7 @@ def main():
     n = args.n
     npy, npz = decomp.choose_decomposition(world, args.decomp)
     ipy, ipz = decomp.rank_position(rank, npy, npz)
-    if args.workload == "iso_mhd":
-        cfg = pcfg.make_config(n, entropy=False, magnetic=True, nu=5e-3, eta=5e-3, cdt=0.4, cdtv=0.3,
-                               nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
-        wname = "isothermal forced MHD turbulence %d^3 (lnrho, uu, aa: 7 vars, FP64)" % n
-    elif args.workload == "hydro_hyper3":
-        cfg = pcfg.config_hydro_hyper3(n, nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
-        wname = "hydro-only forced turbulence %d^3 with 6th-order hyperdiffusion (4 vars, FP64)" % n
-    else:
-        cfg = pcfg.config_mhd_entropy(n, nprocy=npy, ipy=ipy, nprocz=npz, ipz=ipz)
-        wname = "periodic MHD with entropy %d^3 (8 vars, FP64)" % n
+    cfg, wname = workload_config(args, n, npy, ipy, npz, ipz)
     cfg["device"] = local_rank
     cfg["kernel_variant"] = args.kernel_variant
     nvar = cfg["nvar"]
@@ -310,26 +345,29 @@ def main():
         except Exception:
             pass
 
+    # ---- decomposition-invariance checksum: global diagnostics of the state after warmup + steps + e2e steps,
+    # reduced on the device over all ranks (sums: ncclAllReduce) -- must agree between N = 1, 2, 4, 8 to ~1e-12
+    g.time_step(fh, dt, False, t, forcing=forcing.draw(dt), diagnostics=True)
+    red = g.get_gpu_reduced_vars()
+    checksum = {k: red[k] for k in ("urms", "umax", "rhom", "brms", "jrms", "abm", "ssm") if k in red}
+    checksum["after_steps"] = args.warmup + args.steps + args.e2e_steps
+
     if world > 1:
         barrier()  # nobody frees ghost planes a neighbour may still be writing to
     g.finalize_GPU()
 
     cpu_baseline = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "mhd_entropy":
-        v, el, cores = cpu_oracle_throughput(256, 16)
-        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                        "sample": "256^3 periodic box, same 8-variable physics, 16 RK3 steps (%.1f s); CPU restatement "
-                                  "(oracle) with g++ -O3 -march=native -fopenmp, not the Fortran binary" % el}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        v, s_per_step, cores, desc = cpu_oracle_throughput(args, 16)
+        cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": wname + ", helical forcing, fixed dt, 2N-RK3",
-                       "decomposition": "1x%dx%d %s" % (npy, npz, "z-slabs" if npy == 1 else "yz-pencils"), "nvar": nvar,
-                       "z_halo": ("none (1 GPU)" if world == 1 else ("peer puts over NVLink (copy engines)" if args.halo == "p2p" and npz > 1 else "NCCL send/recv")),
-                       "l2": "inputs larger than L2 (%.1f GB per f buffer per GPU)" % (nbytes_f / 1e9),
-                       "kernel_variant": args.kernel_variant, "finite": finite},
+            "config": config_dict(args, world, wname, nvar, nbytes_f),
+            "z_halo": ("none (1 GPU)" if world == 1 else ("peer puts over NVLink (copy engines)" if args.halo == "p2p" and npz > 1 else "NCCL send/recv")),
+            "kernel_variant": args.kernel_variant, "finite": finite, "checksum": checksum,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes_f * world,
                     "d2h_bytes_per_step": nbytes_f * world, "steps": args.e2e_steps,
                     "ms_per_step": ms_e2e / args.e2e_steps,

@@ -493,6 +493,8 @@ static void derive_pars() {
   P.cp = 1 / P.cp1; // p%cp=1/cp1 (eos_idealgas.f90:811)
   P.TT0_1 = std::exp(-P.lnTT0);
   { double fact = 1.0; for (int n = 0; n < 14; ++n) { if (n) fact *= n; P.expc[n] = 1.0 / fact; } }
+  P.expk[0] = 46.16624130844683; P.expk[1] = -0.02166084938653512; P.expk[2] = -5.9631716539705866e-12;
+  for (int j = 0; j < 32; ++j) { P.exptab[j] = (double)exp2l((long double)j / 32.0L); P.exptab[32 + j] = (double)exp2l(-(long double)j / 32.0L); }
   P.mu0 = c.mu0; P.mu01 = 1. / c.mu0;
   P.nu = c.nu; P.nu_hyper3 = c.nu_hyper3; P.diffrho_hyper3 = c.diffrho_hyper3; P.chi = c.chi; P.eta = c.eta;
   P.cdt = c.cdt; P.cdtv = c.cdtv; P.cdtv2 = c.cdtv2; P.cdtv3 = c.cdtv3;
@@ -502,6 +504,7 @@ static void derive_pars() {
   P.lheatc_chiconst = c.lheatc_chiconst; P.lviscosity_heat = c.lviscosity_heat;
   P.lresi_eta_const = c.lresi_eta_const; P.lohmic_heat = c.lohmic_heat; P.llorentzforce = c.llorentzforce;
   P.lupw_uu = c.lupw_uu; P.lupw_lnrho = c.lupw_lnrho; P.lupw_ss = c.lupw_ss; P.lupw_aa = c.lupw_aa;
+  P.mcs20g1 = -(P.cs20 * P.gamma1); P.chicp = P.chi * P.cp; P.nu2 = 2 * P.nu; P.etamu0 = P.eta * P.mu0; P.nu13 = P.nu * (1. / 3.);
   for (int i = 0; i < 3; ++i) P.dmcu[i] = c.lvisc_nu_const ? (c.nu * (1. / 3.)) * P.dmc[0][i] : 0.0;
 }
 
@@ -606,10 +609,15 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v9(c
     CK(cudaFuncSetAttribute(rhs_update_v9<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
     attr_set = true;
   }
-  V2Args v;
-  v.fin = a.fin; v.fout = a.fout; v.df = a.df; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
+  V9Args v;
+  v.fin = a.fin; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
   v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
-  v.df_prefetch = 0;
+  for (int k = 0; k < MAXVAR; ++k) {
+    const bool del = k < 3 || (ENT && MAG && k == 4); // finalised three planes late (pcb200_v9.cuh)
+    const long long off = (long long)std::min(k, NV - 1) * S.P.sv - (del ? NG * S.P.sz : 0);
+    v.df_k[k] = a.df + off;
+    v.fo_k[k] = a.fout + off;
+  }
   const int gx = (S.P.nx + V2_TX - 1) / V2_TX, gy = (S.P.ny + V2_TY - 1) / V2_TY;
   const int nzr = a.z_hi - a.z_lo;
   // one CTA per SM; every z chunk pays 6 extra stages (3 warm-up + 3 cool-down, each ~1/4 of an evaluated plane):

@@ -35,12 +35,15 @@ struct Pars {
   double d1c[3][3];     // d1fac * (45, -9, 1)
   double d2c[3][4];     // d2fac * (-490, 270, -27, 2)/180
   double dmc[3][3];     // dmfac * (270, -27, 2)
+  double mcs20g1, chicp, nu2, etamu0, nu13; // -cs20/gamma, chi*cp, 2 nu, eta*mu0, nu/3 (variant 9: no loop-invariant products in registers)
   double dmcu[3];       // (nu/3) * dmc[0][:] (variant 9: z-mixed part of grad div u scattered straight into du/dt)
   double d2c0x2, d2c0x3; // 2x / 3x the centre weight of der2 (isotropic grids: second derivatives summed over directions)
   double dline_1[3];
   double dxyz_2, dxyz_4, dxyz_6;
   double cs20, gamma, gamma1, gamma_m1, cp, cp1, cv1, lnrho0, lnTT0, TT0_1; // TT0_1 = exp(-lnTT0)
   double expc[14];      // 1/n!, n = 0..13 (exp_fast)
+  double expk[3];       // 32/ln2, -(ln2/32) high part (32 bits), -(ln2/32) low part
+  double exptab[64];    // 2^(j/32), j = 0..31, then 2^(-j/32) (variant 9: table-based exp, copied to shared memory)
   double mu0, mu01;
   double nu, nu_hyper3, diffrho_hyper3, chi, eta;
   double cdt, cdtv, cdtv2, cdtv3, dt1_init;

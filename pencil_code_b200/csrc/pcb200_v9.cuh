@@ -31,7 +31,7 @@ constexpr int V9_NSLOT = 6; // planes z..z+3 in use + 2 in flight
 template <int NV> struct V9Layout {
   static constexpr int SLOT = ((NV * V2_PLANE + 15) / 16) * 16; // doubles per slot (TMA destination: 128-byte aligned)
   static constexpr unsigned TX_BYTES = NV * V2_PLANE * 8;
-  static constexpr size_t SMEM_BYTES = (size_t)V9_NSLOT * SLOT * 8 + V9_NSLOT * 8 + 64;
+  static constexpr size_t SMEM_BYTES = (size_t)V9_NSLOT * SLOT * 8 + V9_NSLOT * 8 + 64 + 64 * 8 + (size_t)NV * V2_THREADS * 8; // + exp table + df staging
 };
 
 // ---- tensor memory as per-thread scratch (shape 32x32b: lane = thread, 32-bit columns).  No "memory" clobber: TMEM
@@ -107,7 +107,97 @@ __device__ __forceinline__ void t9_ld8x2(uint32_t ta, uint32_t tb, double h[8], 
         "=d"(g[2]), "=d"(g[3]), "=d"(g[4]), "=d"(g[5]), "=d"(g[6]), "=d"(g[7])
       : "r"(ta), "r"(tb));
 }
+// two 8-column loads behind one wait
+__device__ __forceinline__ void t9_ld4x2(uint32_t ta, uint32_t tb, double h[4], double g[4]) {
+  asm volatile(
+      "{\n\t.reg .b32 t<16>;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {t0, t1, t2, t3, t4, t5, t6, t7}, [%8];\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {t8, t9, t10, t11, t12, t13, t14, t15}, [%9];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 %0, {t0, t1};\n\tmov.b64 %1, {t2, t3};\n\tmov.b64 %2, {t4, t5};\n\tmov.b64 %3, {t6, t7};\n\t"
+      "mov.b64 %4, {t8, t9};\n\tmov.b64 %5, {t10, t11};\n\tmov.b64 %6, {t12, t13};\n\tmov.b64 %7, {t14, t15};\n\t}"
+      : "=d"(h[0]), "=d"(h[1]), "=d"(h[2]), "=d"(h[3]), "=d"(g[0]), "=d"(g[1]), "=d"(g[2]), "=d"(g[3])
+      : "r"(ta), "r"(tb));
+}
+__device__ __forceinline__ void t9_ld4(uint32_t ta, double h[4]) {
+  asm volatile(
+      "{\n\t.reg .b32 t<8>;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {t0, t1, t2, t3, t4, t5, t6, t7}, [%4];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 %0, {t0, t1};\n\tmov.b64 %1, {t2, t3};\n\tmov.b64 %2, {t4, t5};\n\tmov.b64 %3, {t6, t7};\n\t}"
+      : "=d"(h[0]), "=d"(h[1]), "=d"(h[2]), "=d"(h[3])
+      : "r"(ta));
+}
 __device__ __forceinline__ void t9_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;"); }
+
+// predicated global stores (the compiler turns `if (c) *p = v;` into a branch around the store, which costs a
+// reconvergence point before the next warp-collective tcgen05 operation)
+__device__ __forceinline__ void st_pred(double *p, double v, bool c) {
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t@q st.global.f64 [%0], %1;\n\t}" ::"l"(p), "d"(v), "r"((int)c) : "memory");
+}
+__device__ __forceinline__ void st_pred_cs(double *p, double v, bool c) {
+  asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t@q st.global.cs.f64 [%0], %1;\n\t}" ::"l"(p), "d"(v), "r"((int)c) : "memory");
+}
+
+// df staging: global -> shared without a register destination (LDGSTS), issued at the top of a stage and read back
+// right before the RK update.  A register load does not work here: with the register file full ptxas sinks the
+// load down to its first use (measured: LDG 14 instructions before the DFMA, long_scoreboard 0.3 -> 1.3 per issue).
+// bytes = 0 writes zeros and reads nothing.
+__device__ __forceinline__ void cp_async8(uint32_t dst, const double *src, bool on) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst), "l"(src), "r"(on ? 8 : 0));
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ double lds_volatile(uint32_t addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  return v;
+}
+
+// exp by table: x = (32 m + j) ln2/32 + r, |r| <= ln2/64; exp(x) = 2^m 2^(j/32) e^r with a degree-6 polynomial
+// (truncation 3.5e-18 relative) and the 32-entry table of 2^(j/32) (and its inverse at +32) in shared memory.
+// ~2 ulp; 11 FP64 operations instead of 18 (exp_fast), and exp(-x) comes with 4 more instead of a reciprocal.
+struct ExpRed {
+  double r;
+  int j, m;
+};
+__device__ __forceinline__ ExpRed exp_reduce(double x) {
+  const double shifter = 6755399441055744.0; // 1.5 * 2^52: the low word of t is rint(x * 32/ln2)
+  const double t = fma(x, cP.expk[0], shifter);
+  const int k = __double2loint(t);
+  const double kd = t - shifter;
+  ExpRed e;
+  e.r = fma(kd, cP.expk[2], fma(kd, cP.expk[1], x)); // ln2/32 in two parts (high part: 32 bits)
+  e.j = k & 31;
+  e.m = k >> 5;
+  return e;
+}
+__device__ __forceinline__ double exp_scale(double v, int m) { // v * 2^m (v normal, result normal)
+  return __hiloint2double(__double2hiint(v) + (m << 20), __double2loint(v));
+}
+// (all coefficients are constant-memory operands of the FMAs: cP.expc[n] = 1/n!)
+__device__ __forceinline__ double exp_tab(double x, const double *tab) {
+  const ExpRed e = exp_reduce(x);
+  double p = cP.expc[6];
+#pragma unroll
+  for (int n = 5; n >= 0; --n) p = fma(p, e.r, cP.expc[n]);
+  return exp_scale(p * tab[e.j], e.m);
+}
+// exp(x) and exp(-x): even and odd part of the polynomial
+__device__ __forceinline__ void exp_tab_pm(double x, const double *tab, double &ep, double &em) {
+  const ExpRed e = exp_reduce(x);
+  const double r2 = e.r * e.r;
+  const double pe = fma(r2, fma(r2, fma(r2, cP.expc[6], cP.expc[4]), cP.expc[2]), cP.expc[0]);
+  const double po = e.r * fma(r2, fma(r2, cP.expc[5], cP.expc[3]), cP.expc[1]);
+  ep = exp_scale((pe + po) * tab[e.j], e.m);
+  em = exp_scale((pe - po) * tab[32 + e.j], -e.m);
+}
+// stencil weights applied as one FMA chain (one operation less than the balanced form of d2_line / SymSum::weighted)
+__device__ __forceinline__ double d2_chain(double c, const double m[3], const double p[3]) {
+  return fma(cP.d2c[0][0], c, fma(cP.d2c[0][1], p[0] + m[0], fma(cP.d2c[0][2], p[1] + m[1], cP.d2c[0][3] * (p[2] + m[2]))));
+}
+__device__ __forceinline__ double sym_chain(const SymSum &s, double c, double c0n) {
+  return fma(c0n, c, fma(cP.d2c[0][1], s.s0, fma(cP.d2c[0][2], s.s1, cP.d2c[0][3] * s.s2)));
+}
 
 // taps of one line: m[i] / p[i] at -(i+1) / +(i+1) along x, y (shared memory, centre plane) or z (TMEM history)
 __device__ __forceinline__ void v9_xline(const double *q, double m[3], double p[3]) {
@@ -142,10 +232,26 @@ __device__ __forceinline__ double v9_dxy(const double *q) {
   return cP.dmc[0][0] * g[0] + (cP.dmc[0][1] * g[1] + cP.dmc[0][2] * g[2]);
 }
 
+// Kernel arguments.  Global addresses are formed as (uniform per-variable base from the parameter bank) + (one
+// per-thread element offset that advances by a plane per stage): the bases live in uniform registers / constant
+// memory, so no per-variable 64-bit offsets are held in vector registers.  The bases of the variables that are
+// finalised three planes late (u, and s with a magnetic field) are shifted by -3 planes.
+struct V9Args {
+  const double *fin;
+  const double *dt_dev;
+  double alpha, beta;
+  int read_df, write_df;
+  int z_lo, z_hi, lz;
+  Forcing frc;
+  double *df_k[MAXVAR];   // df + k*sv (- 3*sz if delayed): read and written
+  double *fo_k[MAXVAR];   // f_out + k*sv (- 3*sz if delayed)
+};
+
 extern __shared__ __align__(1024) double v9_smem[];
+template <int V> struct cuda_std_ic { static constexpr int value = V; }; // tag for the stage specialisations
 
 template <bool ENT, bool MAG, bool HYP, bool UPW>
-__global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_constant__ CUtensorMap tmap, const V2Args a) {
+__global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ V9Args a) {
   typedef Slots<ENT> S;
   constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
   constexpr int NGRP = MAG ? 2 : 1;   // vector fields with a grad div: u (and A)
@@ -156,6 +262,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
   double *planes = v9_smem;
   uint64_t *bars = reinterpret_cast<uint64_t *>(planes + V9_NSLOT * L::SLOT);
   uint32_t *tm_slot = reinterpret_cast<uint32_t *>(bars + V9_NSLOT);
+  double *exptab = reinterpret_cast<double *>(bars + V9_NSLOT + 2); // 64 doubles: 2^(j/32), 2^(-j/32)
+  double *dfs = exptab + 64;                                         // [NV][256]: df of this thread's cells
 
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * V2_TX + tx;
   const int bx0 = blockIdx.x * V2_TX, by0 = blockIdx.y * V2_TY; // origin of the halo'd tile (incl. ghosts)
@@ -173,6 +281,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
+  if (tid >= 64 && tid < 128) exptab[tid - 64] = P.exptab[tid - 64];
   if (tid < 32) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tm_slot)) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -194,12 +303,14 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
 
   // TMEM columns of this thread (two warps share each lane quarter -> 256 columns each):
   //   [0,96)    z histories: variable k at 12k, entries f(z-3..z+2)
-  //   [96,224)  accumulator ring: the output plane of stage index i owns the 16 columns at 96 + 16 (i & 7):
-  //             {U0, U1, U2, -, A0, A1, A2, -}: sums for du/dt (scaled by nu/3) and for mu0 j;
-  //             U3 / A3 carry 1/rho and eta mu0/(rho T) of the plane from its centre stage on
+  //   [96,160)  accumulator ring of u: the output plane of stage index i owns the 8 columns at 96 + 8 (i & 7):
+  //             {U0, U1, U2, 1/rho}: sums for du/dt (z-mixed part scaled by nu/3); 1/rho from the centre stage on
+  //   [160,224) accumulator ring of A at 160 + 8 (i & 7): {A0, A1, A2, eta mu0/(rho T)}: sums for mu0 j
   //   [224,256) {partial ds/dt, b_x, b_y, b_z} of the planes z-3..z: stage index i at 224 + 8 (i & 3)
-  const uint32_t tmb = *tm_slot + ((uint32_t)((tid >> 5) & 3) << 21) + (uint32_t)(tid >> 7) * 256u;
-  const uint32_t tmh = tmb, tma = tmb + 96u, tmp = tmb + 224u;
+  // warp-uniform by construction; the shuffle tells the compiler so (TMEM addresses are uniform-register operands:
+  // without it every ring address is computed in vector registers and moved over with R2UR, 31 per stage)
+  const uint32_t tmb = __shfl_sync(0xffffffffu, *tm_slot + ((uint32_t)((tid >> 5) & 3) << 21) + (uint32_t)(tid >> 7) * 256u, 0);
+  const uint32_t tmh = tmb, tmau = tmb + 96u, tmaa = tmb + 160u, tmp = tmb + 224u;
 
   const int toff = (ty + NG) * V2_HX + (tx + NG);
   const long long sv = P.sv, sz = P.sz;
@@ -216,29 +327,67 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
     }
   }
 
+  const uint32_t dfs_u32 = smem_u32(dfs) + (uint32_t)tid * 8u;
+  auto dfv = [&](int k) { return a.read_df ? lds_volatile(dfs_u32 + (uint32_t)k * (V2_THREADS * 8u)) : 0.0; };
   const double dtb = (*a.dt_dev) * a.beta;
   const bool rdf = a.read_df != 0 && active;
-  // running pointers (advance by one plane per stage): cell (ix, iy) of the centre plane of the stage, variable 0
-  const long long o0 = ix + P.sy * iy + sz * (zc0 - NG);
-  double *pdf = a.df + o0, *pfo = a.fout + o0;
-  double fxy_r = 0.0, fxy_i = 0.0; // helical forcing: fx(x)*fy(y) of this thread
-  if (a.frc.on) {
-    const double2 fx = a.frc.fx[ixc], fy = a.frc.fy[iyc];
-    fxy_r = fx.x * fy.x - fx.y * fy.y;
-    fxy_i = fx.x * fy.y + fx.y * fy.x;
-  }
+  // running element offset (advances by one plane per stage): cell (ix, iy) of the centre plane of the stage
+  long long o = ix + P.sy * iy + sz * (zc0 - NG);
   // 2N-RK3 update of one variable (timestep.f90:113,160-161); off = offset from the running pointers
-  auto rk = [&](double r, double dfo, double fcv, long long off, double extra) {
+  // (arithmetic unconditional, only the two stores are predicated: no divergent branch, no reconvergence)
+  auto rk = [&](bool on, double r, double dfo, double fcv, int k, double extra) {
     const double d = a.alpha * dfo + r;
-    if (a.write_df) __stcs(pdf + off, d);
-    pfo[off] = (fcv + dtb * d) + extra;
+    const double fn = (fcv + dtb * d) + extra;
+    st_pred_cs(a.df_k[k] + o, d, on && a.write_df);
+    st_pred(a.fo_k[k] + o, fn, on);
   };
 
+  // Accumulator ring of one vector field (base: its TMEM columns): this plane is z+k of the output planes centre-k and
+  // z-k of the output planes centre+k:  sum_k w_k [E_k(z+k) - E_k(z-k)]  ->  slot(centre-k) += w_k E_k,
+  // slot(centre+k) -= w_k E_k.  Slot centre-3 is complete afterwards (it is read back and finalised at the end of the stage), the slot of
+  // the centre plane is updated by ring_centre, the slot of plane centre+3 is started here.
+  auto ring_scatter = [&](uint32_t base, int j, const double (&E)[3][3], const double w[3]) {
+    auto at = [&](int d) { return base + 8u * (uint32_t)((j + d) & 7); };
+    double s0[4], s1[4];
+    t9_ld4x2(at(-3), at(-2), s0, s1);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      s0[c] = fma(w[2], E[c][2], s0[c]);
+      s1[c] = fma(w[1], E[c][1], s1[c]);
+    }
+    t9_st4(at(-3), s0[0], s0[1], s0[2], s0[3]);
+    t9_st4(at(-2), s1[0], s1[1], s1[2], s1[3]);
+    t9_ld4x2(at(-1), at(1), s0, s1);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      s0[c] = fma(w[0], E[c][0], s0[c]);
+      s1[c] = fma(-w[0], E[c][0], s1[c]);
+    }
+    t9_st4(at(-1), s0[0], s0[1], s0[2], s0[3]);
+    t9_st4(at(1), s1[0], s1[1], s1[2], s1[3]);
+    t9_ld4(at(2), s0);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) s0[c] = fma(-w[1], E[c][1], s0[c]);
+    t9_st4(at(2), s0[0], s0[1], s0[2], s0[3]);
+    t9_st4(at(3), -w[2] * E[0][2], -w[2] * E[1][2], -w[2] * E[2][2], 0.0);
+  };
+  // the slot of the centre plane receives the plane's own part and its `info` entry
+  auto ring_centre = [&](uint32_t base, int j, const double part[3], double info) {
+    const uint32_t ta = base + 8u * (uint32_t)(j & 7);
+    double s0[4];
+    t9_ld4(ta, s0);
+    t9_st4(ta, s0[0] + part[0], s0[1] + part[1], s0[2] + part[2], info);
+  };
+  const double wu[3] = {P.dmcu[0], P.dmcu[1], P.dmcu[2]}, wa[3] = {P.dmc[0][0], P.dmc[0][1], P.dmc[0][2]};
+
   int slot = 0, par = 0;
-#pragma unroll 1
-  for (int j = 0; j < nst; ++j) {
-    const bool full = j >= NG && j < nst - NG; // centre plane inside [zc0, zc1): evaluate it
-    const bool fin = j >= 2 * NG;              // plane (centre - 3) >= zc0: finalise it
+  // One stage = one centre plane.  MODE 0: warm-up (planes zc0-3..zc0-1: in-plane differences only), 1: evaluated
+  // plane, 2: cool-down (planes zc1..zc1+2: differences + finalisation).  Three specialised copies, so the main
+  // loop is straight-line code.
+  auto stage = [&](auto mode_tag, const int j) {
+    constexpr int MODE = decltype(mode_tag)::value;
+    constexpr bool full = MODE == 1;
+    const bool fin = MODE != 0 && j >= 2 * NG; // plane (centre - 3) >= zc0: finalise it (gates memory operations only)
     // slot release + TMA issue: the first warp waits until every warp has finished stage j-1, then refills its slot.
     // Eight rotating named barriers: a warp can be at most 5 stages ahead of the slowest one.
     if (tid < 32 && j > 0) {
@@ -246,18 +395,23 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
       if (tid == 0) issue(j - 1 + V9_NSLOT);
       __syncwarp();
     }
-    // early global loads: df of the planes written in this stage
-    double dfv[NV];
+    // early global loads: df of the planes written in this stage (L2-prefetched two stages earlier).  All at the
+    // top of the stage: issued later they are still in flight when the shared-memory and TMEM loads that share their
+    // scoreboard slots are consumed (measured: long_scoreboard 0.3 -> 1.5 stall cycles per issue).
+    if (a.read_df) {
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const bool del = (k < 3) || (SDEL && k == S::ISS);
-      const bool on = rdf && (del ? fin : full);
-      dfv[k] = on ? __ldg(pdf + k * sv - (del ? NG * sz : 0)) : 0.0;
+      for (int k = 0; k < NV; ++k) {
+        const bool del = (k < 3) || (SDEL && k == S::ISS);
+        const bool on = rdf && (del ? fin : full);
+        cp_async8(dfs_u32 + (uint32_t)k * (V2_THREADS * 8u), a.df_k[k] + o, on);
+      }
     }
     double2 fzv = make_double2(0.0, 0.0);
-    if (a.frc.on && fin) fzv = __ldg(a.frc.fz + (zc0 - 2 * NG + j));
+    if (MODE != 0 && a.frc.on && fin) fzv = __ldg(a.frc.fz + (zc0 - 2 * NG + j));
 
-    mbar_wait(&bars[slot], par);
+    // the slot of this stage's centre plane was already waited for three stages ago (as the newest plane of an
+    // evaluated stage), except in the first six stages of the chunk
+    if (j < 2 * NG) mbar_wait(&bars[slot], par);
     const double *cp = planes + slot * L::SLOT + toff;
     t9_wait_st(); // TMEM stores of the previous stage are complete
 
@@ -310,7 +464,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
             if (UPW) upw_l += au[jd] * (P.d6upfac[0] * r6);
           }
         }
-        if (ENT) del2lnrho = sl.weighted(lnrho, P.d2c0x3);
+        if (ENT) del2lnrho = sym_chain(sl, lnrho, P.d2c0x3);
       }
 
       // ---------------- velocity (hydro.f90:3925-4063, sub.f90:2610-2749)
@@ -349,7 +503,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
           if (jd != i) {
             su.add(m, pp); // the two off-diagonal second derivatives only enter through their sum
           } else {
-            const double d2 = d2_line(u[i], m, pp, 0);
+            const double d2 = d2_chain(u[i], m, pp);
             d2s += d2;
             gdu[i] = d2; // fjji(i,i)=der2 (sub.f90:2651-2653)
           }
@@ -362,9 +516,10 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
             if (UPW) upw_u[i] += au[jd] * (P.d6upfac[0] * r6);
           }
         }
-        d2s += su.weighted(u[i], P.d2c0x2);
+        d2s += sym_chain(su, u[i], P.d2c0x2);
         del2u[i] = d2s;
       }
+      ring_scatter(tmau, j, Eg[0], wu);
       // xy parts of grad div u (the z-mixed parts arrive through the accumulator ring)
       gdu[0] += v9_dxy(cp + (S::IUX + 1) * V2_PLANE);
       gdu[1] += v9_dxy(cp + (S::IUX + 0) * V2_PLANE);
@@ -409,7 +564,8 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
       // continuity (density.f90:2887-3060, 3197-3288)
       double rl = (-divu) - uglnrho;
       if (HYP && P.ldiff_hyper3lnrho) rl += P.diffrho_hyper3 * del6lnrho;
-      if (active) rk(rl, dfv[S::ILN], lnrho, S::ILN * sv, 0.0);
+      cp_async_wait_all(); // df of this stage (issued at its top)
+      rk(active, rl, dfv(S::ILN), lnrho, S::ILN, 0.0);
 
       // eos + energy (eos_idealgas.f90:851-888, entropy.f90:3554-3876, 4852-4947)
       double rs = 0.0, TT1 = 0.0;
@@ -428,31 +584,34 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
           sss.add(m, pp);
           if (UPW) upw_s += au[jd] * (P.d6upfac[0] * d6raw_line(ss, m, pp));
         }
-        del2ss = sss.weighted(ss, P.d2c0x3);
+        del2ss = sym_chain(sss, ss, P.d2c0x3);
         const double e = P.cv1 * ss + P.gamma_m1 * (lnrho - P.lnrho0);
-        const double ex = exp_fast(e);
-        const double cs2 = P.cs20 * ex;
-        TT1 = P.TT0_1 * __drcp_rn(ex);
+        double ex, exm;
+        exp_tab_pm(e, exptab, ex, exm);
+        const double mcs2g = P.mcs20g1 * ex; // -cs2/gamma
+        TT1 = P.TT0_1 * exm;                            // exp(-(lnTT0+e)) (eos_idealgas.f90:851-888)
         double g2 = 0.0;
 #pragma unroll
         for (int jd = 0; jd < 3; ++jd) {
           const double glnTT = P.gamma_m1 * gl[jd] + P.cv1 * gss[jd];
-          ru[jd] += -cs2 * (gl[jd] + glnTT) * P.gamma1;
-          g2 += (gl[jd] + glnTT) * glnTT;
+          const double gsum = gl[jd] + glnTT;
+          ru[jd] = fma(mcs2g, gsum, ru[jd]); // fpres = -cs2*(glnrho+glnTT)/gamma (entropy.f90:3596-3600)
+          g2 = fma(gsum, glnTT, g2);
         }
         double ugss = u[0] * gss[0] + u[1] * gss[1] + u[2] * gss[2];
         if (UPW && P.lupw_ss) ugss -= upw_s;
         rs = -ugss;
-        if (P.lviscosity_heat) rs += TT1 * (2 * P.nu * sij2);
-        if (P.lheatc_chiconst) rs += P.chi * P.cp * ((P.gamma_m1 * del2lnrho + P.cv1 * del2ss) + g2);
-        if (!SDEL && active) rk(rs, dfv[S::ISS], ss, S::ISS * sv, 0.0);
+        if (P.lviscosity_heat) rs += TT1 * (P.nu2 * sij2);
+        if (P.lheatc_chiconst) rs += P.chicp * ((P.gamma_m1 * del2lnrho + P.cv1 * del2ss) + g2);
+        if (!SDEL) rk(active, rs, dfv(S::ISS), ss, S::ISS, 0.0);
       } else {
 #pragma unroll
         for (int jd = 0; jd < 3; ++jd) ru[jd] += -P.cs20 * gl[jd];
       }
-      // everything of du/dt except the z-mixed part of grad div u and the Lorentz force
-#pragma unroll
-      for (int c = 0; c < 3; ++c) part[0][c] = ru[c];
+      // everything of du/dt except the z-mixed part of grad div u and the Lorentz force -> accumulator ring of u
+      if (MAG) rho1 = exp_tab(-lnrho, exptab); // density.f90:2750
+      hT = (MAG && ENT && P.lohmic_heat) ? P.etamu0 * (rho1 * TT1) : 0.0;
+      ring_centre(tmau, j, ru, rho1);
 
       // ---------------- magnetic (magnetic.f90:4279-5225, 5392-6640)
       if (MAG) {
@@ -486,11 +645,11 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
               for (int k = 0; k < 3; ++k) Eg[NGRP - 1][2][k] = dxx[k] + (pp[k] - m[k]);
             }
             aij[i][jd] = (i != jd || upa) ? d1_line(m, pp, 0) : 0.0;
-            if (jd == i) dia[i] = d2_line(av[i], m, pp, 0);
+            if (jd == i) dia[i] = d2_chain(av[i], m, pp);
             else sa.add(m, pp);
             if (UPW && jd != i) upw_a[i] += au[jd] * (P.d6upfac[0] * d6raw_line(av[i], m, pp)); // mask=i (magnetic.f90:6301)
           }
-          rest[i] = sa.weighted(av[i], P.d2c0x2);
+          rest[i] = sym_chain(sa, av[i], P.d2c0x2);
         }
         const double bb[3] = {aij[2][1] - aij[1][2], aij[0][2] - aij[2][0], aij[1][0] - aij[0][1]};
         // mu0 j = grad div A - del2 A: everything but the z-mixed parts
@@ -517,14 +676,12 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
             ra[jd] = (x + upw_a[jd]) + fres[jd];
           }
         }
-        if (active) {
 #pragma unroll
-          for (int i = 0; i < 3; ++i) rk(ra[i], dfv[S::IAX + i], av[i], (S::IAX + i) * sv, 0.0);
-        }
+        for (int i = 0; i < 3; ++i) rk(active, ra[i], dfv(S::IAX + i), av[i], S::IAX + i, 0.0);
         // what the Lorentz force and the Ohmic heating of this plane need three stages from now
-        rho1 = exp_fast(-lnrho); // density.f90:2750
-        hT = (ENT && P.lohmic_heat) ? P.eta * P.mu0 * rho1 * TT1 : 0.0;
         t9_st4(tmp + 8u * (uint32_t)(j & 3), rs, bb[0], bb[1], bb[2]);
+        ring_scatter(tmaa, j, Eg[NGRP - 1], wa);
+        ring_centre(tmaa, j, part[NGRP - 1], hT);
       }
     } else {
       // warm-up / cool-down stage: only the in-plane differences of this plane
@@ -545,7 +702,9 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
 #pragma unroll
         for (int k = 0; k < 3; ++k) Eg[g][2][k] = d[k] + (pp[k] - m[k]);
       }
-      if (fin) { // cool-down: the histories stopped at planes zc1-3..zc1+2
+      ring_scatter(tmau, j, Eg[0], wu);
+      if (MAG) ring_scatter(tmaa, j, Eg[NGRP - 1], wa);
+      if (MODE == 2) { // cool-down: the histories stopped at planes zc1-3..zc1+2
         const uint32_t e = 2u * (uint32_t)(j - (nst - NG));
 #pragma unroll
         for (int i = 0; i < 3; ++i) fq[i] = t9_ld1(tmh + 12u * (S::IUX + i) + e);
@@ -553,57 +712,16 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
       }
     }
 
-    // ---------------- accumulator ring: this plane is z+k of the output planes z = centre-k and z-k of centre+k
-    //   sum_k w_k [E_k(z+k) - E_k(z-k)]  ->  slot(centre-k) += w_k E_k,  slot(centre+k) -= w_k E_k
-    double sA[8], sB[8];
-    const double wu[3] = {P.dmcu[0], P.dmcu[1], P.dmcu[2]}, wa[3] = {P.dmc[0][0], P.dmc[0][1], P.dmc[0][2]};
-    auto slot_of = [&](int d) { return tma + 16u * (uint32_t)((j + d) & 7); };
-    auto upd = [&](double s[8], int k, double sign) { // k = 1..3
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        s[c] = fma(sign * wu[k - 1], Eg[0][c][k - 1], s[c]);
-        if (MAG) s[4 + c] = fma(sign * wa[k - 1], Eg[NGRP - 1][c][k - 1], s[4 + c]);
-      }
-    };
-    // planes centre-3 (complete after this update) and centre-2
-    t9_ld8x2(slot_of(-3), slot_of(-2), sA, sB);
-    upd(sA, 3, 1.0);
-    upd(sB, 2, 1.0);
-    t9_st8(slot_of(-2), sB);
+    // the slots of plane centre-3 are complete: all six neighbouring planes have contributed
+    double sA[4], sB[4];
+    t9_wait_st();
+    t9_ld4x2(tmau + 8u * (uint32_t)((j - 3) & 7), tmaa + 8u * (uint32_t)((j - 3) & 7), sA, sB);
     double rr[3] = {sA[0], sA[1], sA[2]};
-    const double jq[3] = {P.mu01 * sA[4], P.mu01 * sA[5], P.mu01 * sA[6]};
-    const double rho1q = sA[3], hTq = sA[7];
-    // planes centre-1 and centre (the centre plane adds its own part)
-    t9_ld8x2(slot_of(-1), slot_of(0), sA, sB);
-    upd(sA, 1, 1.0);
-    t9_st8(slot_of(-1), sA);
-    if (full) {
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        sB[c] += part[0][c];
-        if (MAG) sB[4 + c] += part[NGRP - 1][c];
-      }
-      sB[3] = rho1;
-      sB[7] = hT;
-      t9_st8(slot_of(0), sB);
-    }
-    // planes centre+1, centre+2 and the new plane centre+3
-    t9_ld8x2(slot_of(1), slot_of(2), sA, sB);
-    upd(sA, 1, -1.0);
-    upd(sB, 2, -1.0);
-    t9_st8(slot_of(1), sA);
-    t9_st8(slot_of(2), sB);
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-      sA[c] = -wu[2] * Eg[0][c][2];
-      sA[4 + c] = MAG ? -wa[2] * Eg[NGRP - 1][c][2] : 0.0;
-    }
-    sA[3] = 0.0;
-    sA[7] = 0.0;
-    t9_st8(slot_of(3), sA);
+    const double jq[3] = {P.mu01 * sB[0], P.mu01 * sB[1], P.mu01 * sB[2]};
+    const double rho1q = sA[3], hTq = sB[3];
 
     // ---------------- finalise plane (centre - 3): all six neighbouring planes have contributed
-    if (fin) {
+    if (MODE != 0) {
       double rsq = 0.0;
       if (MAG) {
         double pd[4];
@@ -621,23 +739,32 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
         rsq = pd[0] + hTq * (jq[0] * jq[0] + jq[1] * jq[1] + jq[2] * jq[2]); // Ohmic heating (magnetic.f90:6138-6144)
       }
       double force[3] = {0., 0., 0.};
-      if (a.frc.on) { // forcing.f90:2170-2345
+      if (a.frc.on) { // forcing.f90:2170-2345; fx(x) fy(y) fz(z) from the tables (substep 3 only)
+        const double2 fx = __ldg(a.frc.fx + ixc), fy = __ldg(a.frc.fy + iyc);
+        const double fxy_r = fx.x * fy.x - fx.y * fy.y, fxy_i = fx.x * fy.y + fx.y * fy.x;
         const double re = fxy_r * fzv.x - fxy_i * fzv.y, im = fxy_r * fzv.y + fxy_i * fzv.x;
 #pragma unroll
         for (int i = 0; i < 3; ++i) force[i] = a.frc.fda[i] * (a.frc.coef1[i] * re - a.frc.coef2[i] * im);
       }
-      if (active) {
+      if (!full) cp_async_wait_all();
 #pragma unroll
-        for (int i = 0; i < 3; ++i) rk(rr[i], dfv[i], fq[i], (S::IUX + i) * sv - NG * sz, force[i]);
-        if (SDEL) rk(rsq, dfv[S::ISS], fq[3], S::ISS * sv - NG * sz, 0.0);
-      }
+      for (int i = 0; i < 3; ++i) rk(active && fin, rr[i], dfv(i), fq[i], S::IUX + i, force[i]);
+      if (SDEL) rk(active && fin, rsq, dfv(S::ISS), fq[3], S::ISS, 0.0);
     }
 
-    pdf += sz;
-    pfo += sz;
+    o += sz;
     if (++slot == V9_NSLOT) { slot = 0; par ^= 1; }
     if (j + 1 < nst && tid >= 32) named_bar_arrive(1 + (j & 7), V2_THREADS);
-  }
+  };
+  typedef cuda_std_ic<0> M0;
+  typedef cuda_std_ic<1> M1;
+  typedef cuda_std_ic<2> M2;
+#pragma unroll 1
+  for (int j = 0; j < NG; ++j) stage(M0(), j);
+#pragma unroll 1
+  for (int j = NG; j < nst - NG; ++j) stage(M1(), j);
+#pragma unroll 1
+  for (int j = nst - NG; j < nst; ++j) stage(M2(), j);
   t9_wait_st();
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();

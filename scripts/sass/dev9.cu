@@ -5,5 +5,5 @@
 #include "pcb200_fast.cuh"
 #include "pcb200_v9.cuh"
 namespace pcb200 {
-template __global__ void rhs_update_v9<true, true, false, false>(const __grid_constant__ CUtensorMap, const V2Args);
+template __global__ void rhs_update_v9<true, true, false, false>(const __grid_constant__ CUtensorMap, const __grid_constant__ V9Args);
 } // namespace pcb200
