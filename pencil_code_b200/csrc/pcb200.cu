@@ -439,6 +439,7 @@ struct State {
   int lforce = 0;
   double coef1[3], coef2[3], fda[3], kk[3], phase = 0, fact = 0, k1_ff = 1;
   double2 *fx_dev = nullptr, *fy_dev = nullptr, *fz_dev = nullptr;
+  double *fpq_dev = nullptr; // Forcing::pq
   // nccl
   ncclComm_t comm = nullptr;
   int rank = 0, nranks = 1;
@@ -917,7 +918,8 @@ static void compute_diagnostics(cudaStream_t st) {
 // Built on the device from scalars passed by value: no host staging buffer, so steps can be queued back to back
 // without a host synchronisation (the tables of step n+1 are written in stream order after step n's kernels).
 __global__ void forcing_tables_kernel(double2 *tab, int mx, int my, int mz, double kx, double ky, double kz, double phase,
-                                      double fact, double x0, double y0, double z0, double dx, double dy, double dz) {
+                                      double fact, double x0, double y0, double z0, double dx, double dy, double dz,
+                                      double *pq, Forcing frc) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= mx + my + mz) return;
   double arg, amp = 1.0;
@@ -927,13 +929,24 @@ __global__ void forcing_tables_kernel(double2 *tab, int mx, int my, int mz, doub
   double sn, cs;
   sincos(arg, &sn, &cs);
   tab[i] = make_double2(cs * amp, sn * amp);
+  if (i >= mx + my) { // per-plane coefficients of variant 9 (Forcing::pq)
+    double *q = pq + 6 * (i - mx - my);
+    for (int c = 0; c < 3; ++c) {
+      q[c] = frc.fda[c] * (frc.coef1[c] * cs - frc.coef2[c] * sn);
+      q[3 + c] = -frc.fda[c] * (frc.coef1[c] * sn + frc.coef2[c] * cs);
+    }
+  }
 }
 static void upload_forcing_tables(cudaStream_t st) {
   const Pars &P = S.P;
   const int n = P.mx + P.my + P.mz;
+  Forcing frc;
+  frc.on = 1;
+  for (int j = 0; j < 3; ++j) { frc.coef1[j] = S.coef1[j]; frc.coef2[j] = S.coef2[j]; frc.fda[j] = S.fda[j]; }
+  frc.fx = frc.fy = frc.fz = nullptr; frc.pq = nullptr;
   forcing_tables_kernel<<<(n + 255) / 256, 256, 0, st>>>(S.fx_dev, P.mx, P.my, P.mz, S.kk[0] * S.k1_ff, S.kk[1] * S.k1_ff,
                                                          S.kk[2] * S.k1_ff, S.phase, S.fact, S.cfg.x0, S.cfg.y0, S.cfg.z0,
-                                                         S.cfg.dx, S.cfg.dy, S.cfg.dz);
+                                                         S.cfg.dx, S.cfg.dy, S.cfg.dz, S.fpq_dev, frc);
   CK(cudaGetLastError());
   S.launches++;
 }
@@ -1242,6 +1255,7 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   CK(cudaMalloc(&S.fx_dev, sizeof(double2) * (P.mx + P.my + P.mz)));
   S.fy_dev = S.fx_dev + P.mx;
   S.fz_dev = S.fy_dev + P.my;
+  CK(cudaMalloc(&S.fpq_dev, sizeof(double) * 6 * P.mz));
   CK(cudaMemcpyToSymbolAsync(cP, &S.P, sizeof(Pars), 0, cudaMemcpyHostToDevice, S.stream));
   S.pinned[0] = S.dt_host;
   CK(cudaMemcpyAsync(S.dt_dev, S.pinned, sizeof(double), cudaMemcpyHostToDevice, S.stream));
@@ -1268,7 +1282,7 @@ extern "C" void finalize_gpu_c(void) {
   if (S.flags) { cudaFree(S.flags); cudaFree(S.seq_slots); }
   cudaFree(S.f[0]); cudaFree(S.f[1]); cudaFree(S.df);
   if (S.ybuf) cudaFree(S.ybuf);
-  cudaFree(S.dt_dev); cudaFree(S.dt1_dev); cudaFree(S.partial); cudaFree(S.diag_dev); cudaFree(S.fx_dev);
+  cudaFree(S.dt_dev); cudaFree(S.dt1_dev); cudaFree(S.partial); cudaFree(S.diag_dev); cudaFree(S.fx_dev); cudaFree(S.fpq_dev);
   cudaFreeHost(S.pinned);
   cudaEventDestroy(S.ev_ready); cudaEventDestroy(S.ev_halo);
   cudaStreamDestroy(S.comm_stream);
@@ -1391,7 +1405,7 @@ extern "C" void rhs_gpu_c(int *isubstep, double *t) {
     upload_forcing_tables(st);
     a.frc.on = 1;
     for (int j = 0; j < 3; ++j) { a.frc.coef1[j] = S.coef1[j]; a.frc.coef2[j] = S.coef2[j]; a.frc.fda[j] = S.fda[j]; }
-    a.frc.fx = S.fx_dev; a.frc.fy = S.fy_dev; a.frc.fz = S.fz_dev;
+    a.frc.fx = S.fx_dev; a.frc.fy = S.fy_dev; a.frc.fz = S.fz_dev; a.frc.pq = S.fpq_dev;
   }
   if (!S.split) {
     wait_halo(st);

@@ -59,6 +59,9 @@ struct Forcing {
   int on;
   double coef1[3], coef2[3], fda[3];
   const double2 *fx, *fy, *fz; // indexed by local index incl. ghosts
+  // variant 9: per-plane coefficients {P_0..2, Q_0..2}(z) with force_i = Re(fx fy) P_i + Im(fx fy) Q_i,
+  // P_i = fda_i (coef1_i Re fz - coef2_i Im fz), Q_i = -fda_i (coef1_i Im fz + coef2_i Re fz)
+  const double *pq;
 };
 
 // ---------------------------------------------------------------------------

@@ -23,6 +23,15 @@
 // Isotropic grids only (dx == dy == dz); arithmetic and reference citations: pcb200_device.cuh / pcb200_fast.cuh.
 #pragma once
 #include "pcb200_fast.cuh"
+#ifndef PCB200_ABL
+#define PCB200_ABL 0
+#endif
+#ifndef V9_DFPF
+#define V9_DFPF 0 // per-thread L2 prefetch of df this many stages ahead (0: off)
+#endif
+#ifndef V9_RING
+#define V9_RING 1 // 1: shifting accumulator slots with static addresses, 0: rotating ring (dynamic addresses)
+#endif
 
 namespace pcb200 {
 
@@ -128,6 +137,69 @@ __device__ __forceinline__ void t9_ld4(uint32_t ta, double h[4]) {
       : "=d"(h[0]), "=d"(h[1]), "=d"(h[2]), "=d"(h[3])
       : "r"(ta));
 }
+
+// ---- accumulator slots of the z-mixed sums ("shift ring", V9_RING=1): position q = 0..5 of a vector field holds the
+// partial sums {c0, c1, c2, info} of the output plane centre + q - 3; every stage adds this plane's contribution and
+// moves each slot one position down, so all addresses are static.  Each block is ONE asm statement whose tcgen05.ld
+// and tcgen05.st name the same registers: the sums are updated in place and the untouched `info` entries ride along
+// (separate load/store statements made ptxas copy every slot through a staging block: 120 moves per cell).
+#define T9_R8(o) "{t" #o "0, t" #o "1, t" #o "2, t" #o "3, t" #o "4, t" #o "5, t" #o "6, t" #o "7}"
+#define T9_FMA(lo, hi, w, e) "mov.b64 d, {" lo ", " hi "};\n\tfma.rn.f64 d, " w ", " e ", d;\n\tmov.b64 {" lo ", " hi "}, d;\n\t"
+// final = old[0] + w3 E3 -> scratch slot (+48); new[0] = old[1] + w2 E2, new[1] = old[2] + w1 E1
+__device__ __forceinline__ void t9_ring_a(uint32_t b, double w1, double w2, double w3, const double (&E)[3][3]) {
+  asm volatile(
+      "{\n\t.reg .b32 ta<8>, tb<8>, tc<8>;\n\t.reg .f64 d;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {ta0, ta1, ta2, ta3, ta4, ta5, ta6, ta7}, [%0];\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {tb0, tb1, tb2, tb3, tb4, tb5, tb6, tb7, tc0, tc1, tc2, tc3, tc4, tc5, tc6, tc7}, [%1];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      T9_FMA("ta0", "ta1", "%5", "%8") T9_FMA("ta2", "ta3", "%5", "%11") T9_FMA("ta4", "ta5", "%5", "%14")
+      T9_FMA("tb0", "tb1", "%4", "%7") T9_FMA("tb2", "tb3", "%4", "%10") T9_FMA("tb4", "tb5", "%4", "%13")
+      T9_FMA("tc0", "tc1", "%3", "%6") T9_FMA("tc2", "tc3", "%3", "%9") T9_FMA("tc4", "tc5", "%3", "%12")
+      "tcgen05.st.sync.aligned.32x32b.x8.b32 [%2], {ta0, ta1, ta2, ta3, ta4, ta5, ta6, ta7};\n\t"
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {tb0, tb1, tb2, tb3, tb4, tb5, tb6, tb7, tc0, tc1, tc2, tc3, tc4, tc5, tc6, tc7};\n\t}"
+      ::"r"(b), "r"(b + 8u), "r"(b + 48u), "d"(w1), "d"(w2), "d"(w3),
+      "d"(E[0][0]), "d"(E[0][1]), "d"(E[0][2]), "d"(E[1][0]), "d"(E[1][1]), "d"(E[1][2]), "d"(E[2][0]), "d"(E[2][1]), "d"(E[2][2]));
+}
+// new[2] = old[3] + part, info; new[3] = old[4] - w1 E1
+__device__ __forceinline__ void t9_ring_b(uint32_t b, double mw1, const double (&E)[3][3], const double part[3], double info) {
+  asm volatile(
+      "{\n\t.reg .b32 tb<8>, tc<8>;\n\t.reg .f64 d;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {tb0, tb1, tb2, tb3, tb4, tb5, tb6, tb7, tc0, tc1, tc2, tc3, tc4, tc5, tc6, tc7}, [%0];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 d, {tb0, tb1};\n\tadd.rn.f64 d, d, %6;\n\tmov.b64 {tb0, tb1}, d;\n\t"
+      "mov.b64 d, {tb2, tb3};\n\tadd.rn.f64 d, d, %7;\n\tmov.b64 {tb2, tb3}, d;\n\t"
+      "mov.b64 d, {tb4, tb5};\n\tadd.rn.f64 d, d, %8;\n\tmov.b64 {tb4, tb5}, d;\n\t"
+      "mov.b64 {tb6, tb7}, %9;\n\t"
+      T9_FMA("tc0", "tc1", "%2", "%3") T9_FMA("tc2", "tc3", "%2", "%4") T9_FMA("tc4", "tc5", "%2", "%5")
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%1], {tb0, tb1, tb2, tb3, tb4, tb5, tb6, tb7, tc0, tc1, tc2, tc3, tc4, tc5, tc6, tc7};\n\t}"
+      ::"r"(b + 24u), "r"(b + 16u), "d"(mw1), "d"(E[0][0]), "d"(E[1][0]), "d"(E[2][0]), "d"(part[0]), "d"(part[1]), "d"(part[2]), "d"(info));
+}
+// new[4] = old[5] - w2 E2; new[5] = -w3 E3
+__device__ __forceinline__ void t9_ring_c(uint32_t b, double mw2, double mw3, const double (&E)[3][3]) {
+  asm volatile(
+      "{\n\t.reg .b32 tb<8>, tc<8>;\n\t.reg .f64 d;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {tb0, tb1, tb2, tb3, tb4, tb5, tb6, tb7}, [%0];\n\t"
+      "mul.rn.f64 d, %3, %7;\n\tmov.b64 {tc0, tc1}, d;\n\t"
+      "mul.rn.f64 d, %3, %8;\n\tmov.b64 {tc2, tc3}, d;\n\t"
+      "mul.rn.f64 d, %3, %9;\n\tmov.b64 {tc4, tc5}, d;\n\t"
+      "mov.b32 tc6, 0;\n\tmov.b32 tc7, 0;\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      T9_FMA("tb0", "tb1", "%2", "%4") T9_FMA("tb2", "tb3", "%2", "%5") T9_FMA("tb4", "tb5", "%2", "%6")
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%1], {tb0, tb1, tb2, tb3, tb4, tb5, tb6, tb7, tc0, tc1, tc2, tc3, tc4, tc5, tc6, tc7};\n\t}"
+      ::"r"(b + 40u), "r"(b + 32u), "d"(mw2), "d"(mw3), "d"(E[0][1]), "d"(E[1][1]), "d"(E[2][1]), "d"(E[0][2]), "d"(E[1][2]), "d"(E[2][2]));
+}
+// slot += a (the pressure force, known only after the entropy section, joins the centre slot at its new position)
+__device__ __forceinline__ void t9_ring_add(uint32_t ta, const double a[3]) {
+  asm volatile(
+      "{\n\t.reg .b32 tb<8>;\n\t.reg .f64 d;\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {tb0, tb1, tb2, tb3, tb4, tb5, tb6, tb7}, [%0];\n\t"
+      "tcgen05.wait::ld.sync.aligned;\n\t"
+      "mov.b64 d, {tb0, tb1};\n\tadd.rn.f64 d, d, %1;\n\tmov.b64 {tb0, tb1}, d;\n\t"
+      "mov.b64 d, {tb2, tb3};\n\tadd.rn.f64 d, d, %2;\n\tmov.b64 {tb2, tb3}, d;\n\t"
+      "mov.b64 d, {tb4, tb5};\n\tadd.rn.f64 d, d, %3;\n\tmov.b64 {tb4, tb5}, d;\n\t"
+      "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {tb0, tb1, tb2, tb3, tb4, tb5, tb6, tb7};\n\t}"
+      ::"r"(ta), "d"(a[0]), "d"(a[1]), "d"(a[2]));
+}
 __device__ __forceinline__ void t9_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;"); }
 
 // predicated global stores (the compiler turns `if (c) *p = v;` into a branch around the store, which costs a
@@ -208,6 +280,7 @@ __device__ __forceinline__ void v9_xline(const double *q, double m[3], double p[
   }
 }
 __device__ __forceinline__ void v9_yline(const double *q, double m[3], double p[3]) {
+  if (PCB200_ABL & 16) { for (int i = 0; i < 3; ++i) { m[i] = q[-(i + 1)] * 1.5; p[i] = q[i + 1] * 0.5; } return; }
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
     m[i] = q[-(i + 1) * V2_HX];
@@ -223,6 +296,7 @@ __device__ __forceinline__ void v9_zline(const double h[7], double m[3], double 
 }
 // bidiagonal xy derivative in the centre plane (deriv.f90:1400-1452)
 __device__ __forceinline__ double v9_dxy(const double *q) {
+  if (PCB200_ABL & 4) return q[0];
   double g[3];
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
@@ -310,7 +384,12 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
   // warp-uniform by construction; the shuffle tells the compiler so (TMEM addresses are uniform-register operands:
   // without it every ring address is computed in vector registers and moved over with R2UR, 31 per stage)
   const uint32_t tmb = __shfl_sync(0xffffffffu, *tm_slot + ((uint32_t)((tid >> 5) & 3) << 21) + (uint32_t)(tid >> 7) * 256u, 0);
+  #if V9_RING
+  //   (shift ring: [96,152) u: six slots of 8 columns + the finished slot at +48, [152,208) A likewise, [208,240) pending)
+  const uint32_t tmh = tmb, tmau = tmb + 96u, tmaa = tmb + 152u, tmp = tmb + 208u;
+#else
   const uint32_t tmh = tmb, tmau = tmb + 96u, tmaa = tmb + 160u, tmp = tmb + 224u;
+#endif
 
   const int toff = (ty + NG) * V2_HX + (tx + NG);
   const long long sv = P.sv, sz = P.sz;
@@ -327,17 +406,24 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
     }
   }
 
+  if (a.frc.on) { // forcing.f90:2170-2345: Re, Im of fx(x) fy(y) of this thread's column -> TMEM columns 240..243
+    const double2 fx = __ldg(a.frc.fx + ixc), fy = __ldg(a.frc.fy + iyc);
+    t9_st2(tmb + 240u, fx.x * fy.x - fx.y * fy.y, fx.x * fy.y + fx.y * fy.x);
+  }
   const uint32_t dfs_u32 = smem_u32(dfs) + (uint32_t)tid * 8u;
-  auto dfv = [&](int k) { return a.read_df ? lds_volatile(dfs_u32 + (uint32_t)k * (V2_THREADS * 8u)) : 0.0; };
+  auto dfv = [&](int k) { if (PCB200_ABL & 32) return a.alpha; return a.read_df ? lds_volatile(dfs_u32 + (uint32_t)k * (V2_THREADS * 8u)) : 0.0; };
   const double dtb = (*a.dt_dev) * a.beta;
   const bool rdf = a.read_df != 0 && active;
   // running element offset (advances by one plane per stage): cell (ix, iy) of the centre plane of the stage
   long long o = ix + P.sy * iy + sz * (zc0 - NG);
+  auto dfn = [&](int) {};
   // 2N-RK3 update of one variable (timestep.f90:113,160-161); off = offset from the running pointers
   // (arithmetic unconditional, only the two stores are predicated: no divergent branch, no reconvergence)
-  auto rk = [&](bool on, double r, double dfo, double fcv, int k, double extra) {
+  auto rk = [&](bool on, double r, double dfo, double fcv, int k, auto extra) {
     const double d = a.alpha * dfo + r;
-    const double fn = (fcv + dtb * d) + extra;
+    double fn = fcv + dtb * d;
+    if (sizeof(extra) == sizeof(double)) fn += extra; // forcing (velocity only); callers without one pass an int
+    if (PCB200_ABL & 8) { if (d == 1.2345 && fn == 6.789) st_pred(a.fo_k[k] + o, fn, on); return; }
     st_pred_cs(a.df_k[k] + o, d, on && a.write_df);
     st_pred(a.fo_k[k] + o, fn, on);
   };
@@ -347,6 +433,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
   // slot(centre+k) -= w_k E_k.  Slot centre-3 is complete afterwards (it is read back and finalised at the end of the stage), the slot of
   // the centre plane is updated by ring_centre, the slot of plane centre+3 is started here.
   auto ring_scatter = [&](uint32_t base, int j, const double (&E)[3][3], const double w[3]) {
+    if (PCB200_ABL & 1) return;
     auto at = [&](int d) { return base + 8u * (uint32_t)((j + d) & 7); };
     double s0[4], s1[4];
     t9_ld4x2(at(-3), at(-2), s0, s1);
@@ -373,6 +460,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
   };
   // the slot of the centre plane receives the plane's own part and its `info` entry
   auto ring_centre = [&](uint32_t base, int j, const double part[3], double info) {
+    if (PCB200_ABL & 1) return;
     const uint32_t ta = base + 8u * (uint32_t)(j & 7);
     double s0[4];
     t9_ld4(ta, s0);
@@ -398,16 +486,23 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
     // early global loads: df of the planes written in this stage (L2-prefetched two stages earlier).  All at the
     // top of the stage: issued later they are still in flight when the shared-memory and TMEM loads that share their
     // scoreboard slots are consumed (measured: long_scoreboard 0.3 -> 1.5 stall cycles per issue).
-    if (a.read_df) {
+    if (a.read_df && !(PCB200_ABL & 32)) {
 #pragma unroll
       for (int k = 0; k < NV; ++k) {
         const bool del = (k < 3) || (SDEL && k == S::ISS);
         const bool on = rdf && (del ? fin : full);
         cp_async8(dfs_u32 + (uint32_t)k * (V2_THREADS * 8u), a.df_k[k] + o, on);
+#if V9_DFPF
+        if (rdf && j + V9_DFPF < nst) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.df_k[k] + (o + V9_DFPF * sz)));
+#endif
       }
     }
-    double2 fzv = make_double2(0.0, 0.0);
-    if (MODE != 0 && a.frc.on && fin) fzv = __ldg(a.frc.fz + (zc0 - 2 * NG + j));
+    double2 fpq[3];
+    if (MODE != 0 && a.frc.on && fin) { // Forcing::pq of the plane that is finalised in this stage
+      const double2 *q2 = reinterpret_cast<const double2 *>(a.frc.pq) + 3 * (zc0 - 2 * NG + j);
+#pragma unroll
+      for (int i = 0; i < 3; ++i) fpq[i] = __ldg(q2 + i);
+    }
 
     // the slot of this stage's centre plane was already waited for three stages ago (as the newest plane of an
     // evaluated stage), except in the first six stages of the chunk
@@ -435,7 +530,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
         t9_ld6(ta, h);
         h[6] = cp3[k * V2_PLANE];
 #pragma unroll
-        for (int e = 0; e < 6; ++e) t9_st1(ta + 2u * e, h[e + 1]);
+        for (int e = 0; e < ((PCB200_ABL & 2) ? 1 : 6); ++e) t9_st1(ta + 2u * e, h[e + 1]);
       };
       double h[7], m[3], pp[3], dxx[3];
       double au[3] = {0., 0., 0.};
@@ -519,7 +614,9 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
         d2s += sym_chain(su, u[i], P.d2c0x2);
         del2u[i] = d2s;
       }
+#if !V9_RING
       ring_scatter(tmau, j, Eg[0], wu);
+#endif
       // xy parts of grad div u (the z-mixed parts arrive through the accumulator ring)
       gdu[0] += v9_dxy(cp + (S::IUX + 1) * V2_PLANE);
       gdu[1] += v9_dxy(cp + (S::IUX + 0) * V2_PLANE);
@@ -561,11 +658,25 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
 #pragma unroll
         for (int i = 0; i < 3; ++i) ru[i] += P.nu_hyper3 * hyp[i];
       }
+#if V9_RING
+      // everything of du/dt that is known now (advection, viscosity; isothermal pressure) -> accumulator slots of u;
+      // with entropy the pressure force follows below (t9_ring_add)
+      if (!ENT) {
+#pragma unroll
+        for (int jd = 0; jd < 3; ++jd) ru[jd] += -P.cs20 * gl[jd];
+      }
+      if (MAG) rho1 = exp_tab(-lnrho, exptab); // density.f90:2750
+      if (!(PCB200_ABL & 1)) {
+        t9_ring_a(tmau, wu[0], wu[1], wu[2], Eg[0]);
+        t9_ring_b(tmau, -wu[0], Eg[0], ru, rho1);
+        t9_ring_c(tmau, -wu[1], -wu[2], Eg[0]);
+      }
+#endif
       // continuity (density.f90:2887-3060, 3197-3288)
       double rl = (-divu) - uglnrho;
       if (HYP && P.ldiff_hyper3lnrho) rl += P.diffrho_hyper3 * del6lnrho;
       cp_async_wait_all(); // df of this stage (issued at its top)
-      rk(active, rl, dfv(S::ILN), lnrho, S::ILN, 0.0);
+      rk(active, rl, dfv(S::ILN), lnrho, S::ILN, 0);
 
       // eos + energy (eos_idealgas.f90:851-888, entropy.f90:3554-3876, 4852-4947)
       double rs = 0.0, TT1 = 0.0;
@@ -595,7 +706,11 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
         for (int jd = 0; jd < 3; ++jd) {
           const double glnTT = P.gamma_m1 * gl[jd] + P.cv1 * gss[jd];
           const double gsum = gl[jd] + glnTT;
-          ru[jd] = fma(mcs2g, gsum, ru[jd]); // fpres = -cs2*(glnrho+glnTT)/gamma (entropy.f90:3596-3600)
+#if V9_RING
+          ru[jd] = mcs2g * gsum; // fpres = -cs2*(glnrho+glnTT)/gamma (entropy.f90:3596-3600)
+#else
+          ru[jd] = fma(mcs2g, gsum, ru[jd]);
+#endif
           g2 = fma(gsum, glnTT, g2);
         }
         double ugss = u[0] * gss[0] + u[1] * gss[1] + u[2] * gss[2];
@@ -603,15 +718,22 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
         rs = -ugss;
         if (P.lviscosity_heat) rs += TT1 * (P.nu2 * sij2);
         if (P.lheatc_chiconst) rs += P.chicp * ((P.gamma_m1 * del2lnrho + P.cv1 * del2ss) + g2);
-        if (!SDEL) rk(active, rs, dfv(S::ISS), ss, S::ISS, 0.0);
+        if (!SDEL) rk(active, rs, dfv(S::ISS), ss, S::ISS, 0);
       } else {
+#if !V9_RING
 #pragma unroll
         for (int jd = 0; jd < 3; ++jd) ru[jd] += -P.cs20 * gl[jd];
+#endif
       }
+#if V9_RING
+      if (ENT && !(PCB200_ABL & 1)) t9_ring_add(tmau + 16u, ru);
+      hT = (MAG && ENT && P.lohmic_heat) ? P.etamu0 * (rho1 * TT1) : 0.0;
+#else
       // everything of du/dt except the z-mixed part of grad div u and the Lorentz force -> accumulator ring of u
       if (MAG) rho1 = exp_tab(-lnrho, exptab); // density.f90:2750
       hT = (MAG && ENT && P.lohmic_heat) ? P.etamu0 * (rho1 * TT1) : 0.0;
       ring_centre(tmau, j, ru, rho1);
+#endif
 
       // ---------------- magnetic (magnetic.f90:4279-5225, 5392-6640)
       if (MAG) {
@@ -677,11 +799,19 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
           }
         }
 #pragma unroll
-        for (int i = 0; i < 3; ++i) rk(active, ra[i], dfv(S::IAX + i), av[i], S::IAX + i, 0.0);
+        for (int i = 0; i < 3; ++i) rk(active, ra[i], dfv(S::IAX + i), av[i], S::IAX + i, 0);
         // what the Lorentz force and the Ohmic heating of this plane need three stages from now
         t9_st4(tmp + 8u * (uint32_t)(j & 3), rs, bb[0], bb[1], bb[2]);
+#if V9_RING
+        if (!(PCB200_ABL & 1)) {
+          t9_ring_a(tmaa, wa[0], wa[1], wa[2], Eg[NGRP - 1]);
+          t9_ring_b(tmaa, -wa[0], Eg[NGRP - 1], part[NGRP - 1], hT);
+          t9_ring_c(tmaa, -wa[1], -wa[2], Eg[NGRP - 1]);
+        }
+#else
         ring_scatter(tmaa, j, Eg[NGRP - 1], wa);
         ring_centre(tmaa, j, part[NGRP - 1], hT);
+#endif
       }
     } else {
       // warm-up / cool-down stage: only the in-plane differences of this plane
@@ -702,8 +832,22 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
 #pragma unroll
         for (int k = 0; k < 3; ++k) Eg[g][2][k] = d[k] + (pp[k] - m[k]);
       }
+#if V9_RING
+      {
+        const double zero3[3] = {0., 0., 0.};
+        t9_ring_a(tmau, wu[0], wu[1], wu[2], Eg[0]);
+        t9_ring_b(tmau, -wu[0], Eg[0], zero3, 0.0);
+        t9_ring_c(tmau, -wu[1], -wu[2], Eg[0]);
+        if (MAG) {
+          t9_ring_a(tmaa, wa[0], wa[1], wa[2], Eg[NGRP - 1]);
+          t9_ring_b(tmaa, -wa[0], Eg[NGRP - 1], zero3, 0.0);
+          t9_ring_c(tmaa, -wa[1], -wa[2], Eg[NGRP - 1]);
+        }
+      }
+#else
       ring_scatter(tmau, j, Eg[0], wu);
       if (MAG) ring_scatter(tmaa, j, Eg[NGRP - 1], wa);
+#endif
       if (MODE == 2) { // cool-down: the histories stopped at planes zc1-3..zc1+2
         const uint32_t e = 2u * (uint32_t)(j - (nst - NG));
 #pragma unroll
@@ -715,7 +859,12 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
     // the slots of plane centre-3 are complete: all six neighbouring planes have contributed
     double sA[4], sB[4];
     t9_wait_st();
-    t9_ld4x2(tmau + 8u * (uint32_t)((j - 3) & 7), tmaa + 8u * (uint32_t)((j - 3) & 7), sA, sB);
+    if (PCB200_ABL & 1) { for (int q = 0; q < 4; ++q) { sA[q] = 1.0; sB[q] = 1.0; } }
+#if V9_RING
+    else t9_ld4x2(tmau + 48u, tmaa + 48u, sA, sB);
+#else
+    else t9_ld4x2(tmau + 8u * (uint32_t)((j - 3) & 7), tmaa + 8u * (uint32_t)((j - 3) & 7), sA, sB);
+#endif
     double rr[3] = {sA[0], sA[1], sA[2]};
     const double jq[3] = {P.mu01 * sB[0], P.mu01 * sB[1], P.mu01 * sB[2]};
     const double rho1q = sA[3], hTq = sB[3];
@@ -726,9 +875,7 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
       if (MAG) {
         double pd[4];
         { // {partial ds/dt, b} written in stage j-3
-          double t6[6];
-          t9_ld6(tmp + 8u * (uint32_t)((j + 1) & 3), t6);
-          pd[0] = t6[0]; pd[1] = t6[1]; pd[2] = t6[2]; pd[3] = t6[3];
+          t9_ld4(tmp + 8u * (uint32_t)((j + 1) & 3), pd);
         }
         const double *bq = pd + 1;
         if (P.llorentzforce) { // jxbr = rho1*(jj x bb) (magnetic.f90:4870-4888, 5531)
@@ -739,17 +886,21 @@ __global__ void __launch_bounds__(V2_THREADS, 1) rhs_update_v9(const __grid_cons
         rsq = pd[0] + hTq * (jq[0] * jq[0] + jq[1] * jq[1] + jq[2] * jq[2]); // Ohmic heating (magnetic.f90:6138-6144)
       }
       double force[3] = {0., 0., 0.};
-      if (a.frc.on) { // forcing.f90:2170-2345; fx(x) fy(y) fz(z) from the tables (substep 3 only)
-        const double2 fx = __ldg(a.frc.fx + ixc), fy = __ldg(a.frc.fy + iyc);
-        const double fxy_r = fx.x * fy.x - fx.y * fy.y, fxy_i = fx.x * fy.y + fx.y * fy.x;
-        const double re = fxy_r * fzv.x - fxy_i * fzv.y, im = fxy_r * fzv.y + fxy_i * fzv.x;
-#pragma unroll
-        for (int i = 0; i < 3; ++i) force[i] = a.frc.fda[i] * (a.frc.coef1[i] * re - a.frc.coef2[i] * im);
+      if (a.frc.on && fin) { // force_i = Re(fx fy) P_i(z) + Im(fx fy) Q_i(z) (substep 3 only)
+        double fxy[2];
+        {
+          double t4[4];
+          t9_ld4(tmb + 240u, t4);
+          fxy[0] = t4[0]; fxy[1] = t4[1];
+        }
+        force[0] = fxy[0] * fpq[0].x + fxy[1] * fpq[1].y;
+        force[1] = fxy[0] * fpq[0].y + fxy[1] * fpq[2].x;
+        force[2] = fxy[0] * fpq[1].x + fxy[1] * fpq[2].y;
       }
       if (!full) cp_async_wait_all();
 #pragma unroll
       for (int i = 0; i < 3; ++i) rk(active && fin, rr[i], dfv(i), fq[i], S::IUX + i, force[i]);
-      if (SDEL) rk(active && fin, rsq, dfv(S::ISS), fq[3], S::ISS, 0.0);
+      if (SDEL) rk(active && fin, rsq, dfv(S::ISS), fq[3], S::ISS, 0);
     }
 
     o += sz;

@@ -278,7 +278,7 @@ def test_p2p_put_path_loopback(oracle_mod, monkeypatch, overlap):
             assert abs(a[k] - b[k]) <= 1e-11 * abs(b[k])
 
 
-@pytest.mark.parametrize("variant", [1, 2, 3, 4, 5, 6, 7, 8])
+@pytest.mark.parametrize("variant", VARIANTS)
 @pytest.mark.parametrize("overlap", [True, False])
 def test_exchange_code_path_loopback(oracle_mod, monkeypatch, variant, overlap):
     """The multi-GPU code path on ONE GPU: PCB200_LOOPBACK=1 makes every neighbour this rank, so the y-face
