@@ -7,6 +7,7 @@
 #include "pcb200_fast.cuh"
 #include "pcb200_v5.cuh"
 #include "pcb200_v9.cuh"
+#include "pcb200_v10.cuh"
 #include <cudaTypedefs.h>
 #include "../../include/pcb200.h"
 
@@ -388,7 +389,11 @@ struct State {
   bool configured = false, initialized = false;
   pcb200_config cfg{};
   Pars P{};
-  size_t nreal = 0; // doubles per f buffer
+  size_t nreal = 0; // doubles per host f-array (mx*my*mz*nvar)
+  size_t ndev = 0;  // doubles per device buffer (row pitch P.sy, + 2 for the shifted base)
+  int xpad = 0;     // variant 10: rows are padded by one double at either end (pitch mx+2, logical base = allocation + 1):
+                    // the first interior cell of a row is then 16-byte aligned, as TMA box starts must be
+  double *f_alloc[2] = {nullptr, nullptr}, *df_alloc = nullptr;
   double *f[2] = {nullptr, nullptr};
   double *df = nullptr;
   int cur = 0;
@@ -397,6 +402,7 @@ struct State {
   CUtensorMap tmap_df;      // df tiles (32 x 8 x 1 x nvar) for L2 prefetch
   CUtensorMap tmap3_ring[2], tmap3_scal[2]; // variant 5: 3-variable and {lnrho,ss} boxes
   CUtensorMap tmap9[2];     // variant 9: one (38 x 14 x 1 x nvar) box per plane
+  CUtensorMap tmap10_i[2], tmap10_o1[2], tmap10_o3[2], tmap10_d1, tmap10_d3; // variant 10: interior boxes of f (in), clipped 1- and 3-variable boxes of f (out) and df
   int variant = 1;          // kernel actually used (1 = global loads, 4 = TMA ring anisotropic, 5 = TMA ring isotropic, 9 = all-trail + TMEM)
   int nsm = 148;
   cudaStream_t stream = nullptr, comm_stream = nullptr;
@@ -463,7 +469,7 @@ static void derive_pars() {
   P.nx = c.nx; P.ny = c.ny; P.nz = c.nz;
   P.mx = c.nx + 2 * NG; P.my = c.ny + 2 * NG; P.mz = c.nz + 2 * NG;
   P.nvar = c.nvar;
-  P.sy = P.mx; P.sz = (long long)P.mx * P.my; P.sv = P.sz * P.mz;
+  P.sy = P.mx + 2 * S.xpad; P.sz = (long long)P.sy * P.my; P.sv = P.sz * P.mz;
   const double d[3] = {c.dx, c.dy, c.dz};
   double d1[3];
   for (int j = 0; j < 3; ++j) {
@@ -529,7 +535,8 @@ static void check_supported() {
 }
 
 // TMA descriptor of one f buffer: 4-D tensor (x,y,z,var), box = one halo'd (38 x 14) plane tile
-static void make_tensor_map(CUtensorMap *tm, double *base, int box_x = V2_HX, int box_y = V2_HY, int box_v = 1) {
+// clip: the tensor ends at the last interior cell in x and y (stores of partial tiles are cut off by the TMA engine)
+static void make_tensor_map(CUtensorMap *tm, double *base, int box_x = V2_HX, int box_y = V2_HY, int box_v = 1, bool clip = false) {
   static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
   if (!encode) {
     cudaDriverEntryPointQueryResult qres;
@@ -539,7 +546,7 @@ static void make_tensor_map(CUtensorMap *tm, double *base, int box_x = V2_HX, in
     encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
   }
   const Pars &P = S.P;
-  cuuint64_t dims[4] = {(cuuint64_t)P.mx, (cuuint64_t)P.my, (cuuint64_t)P.mz, (cuuint64_t)P.nvar};
+  cuuint64_t dims[4] = {(cuuint64_t)(clip ? P.nx + NG + S.xpad : P.sy), (cuuint64_t)(clip ? P.ny + NG : P.my), (cuuint64_t)P.mz, (cuuint64_t)P.nvar};
   cuuint64_t strides[3] = {(cuuint64_t)P.sy * 8, (cuuint64_t)P.sz * 8, (cuuint64_t)P.sv * 8};
   cuuint32_t box[4] = {(cuuint32_t)box_x, (cuuint32_t)box_y, 1, (cuuint32_t)box_v};
   cuuint32_t estr[4] = {1, 1, 1, 1};
@@ -642,6 +649,42 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v9(c
   rhs_update_v9<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(S.tmap9[w], v);
 }
 
+template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v10(const UpdateArgs &a, cudaStream_t st) {
+  constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
+  typedef V10Layout<NV> L;
+  static bool attr_set = false;
+  if (!attr_set) {
+    CK(cudaFuncSetAttribute(rhs_update_v10<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
+    attr_set = true;
+  }
+  V10Args v;
+  v.fin = a.fin; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
+  v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
+  const int gx = (S.P.nx + V2_TX - 1) / V2_TX, gy = (S.P.ny + V2_TY - 1) / V2_TY;
+  const int nzr = a.z_hi - a.z_lo;
+  // one CTA per SM; every z chunk pays 6 extra stages (3 warm-up + 3 cool-down, each ~1/4 of an evaluated plane):
+  // among the chunk counts that give at least one full wave take the one with the best (wave fill) x (chunk efficiency)
+  int pick = 1;
+  {
+    double best = 0.0;
+    const int tiles = gx * gy;
+    const int cmax = std::max(1, nzr / 8);
+    for (int c = 1; c <= cmax && tiles * c <= 16 * S.nsm; ++c) {
+      const int lz = (nzr + c - 1) / c;
+      const double waves = (double)tiles * ((nzr + lz - 1) / lz) / S.nsm;
+      const double eff = waves / std::ceil(waves) * (lz / (lz + 1.5));
+      if (eff > best + 0.01) { best = eff; pick = c; }
+    }
+  }
+  v.lz = (nzr + pick - 1) / pick;
+  const int nch = (nzr + v.lz - 1) / v.lz;
+  dim3 g(gx, gy, nch), b(V2_TX, V10_CTA / V2_TX, 1); // eight compute warps (+ the producer warpgroup)
+  const int w = (a.fin == S.f[0]) ? 0 : 1;
+  V10Maps tm;
+  tm.h = S.tmap9[w]; tm.i = S.tmap10_i[w]; tm.d1 = S.tmap10_d1; tm.d3 = S.tmap10_d3; tm.o1 = S.tmap10_o1[w ^ 1]; tm.o3 = S.tmap10_o3[w ^ 1];
+  rhs_update_v10<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(tm, v);
+}
+
 static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   if (a.z_hi <= a.z_lo) return;
   const bool ent = S.cfg.iss >= 0, mag = S.cfg.iax >= 0;
@@ -660,7 +703,8 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
   }
 #define DISPATCH(E, M, H, U)                                   \
   do {                                                         \
-    if (S.variant == 9) launch_update_v9<E, M, H, U>(a, st); \
+    if (S.variant == 10) launch_update_v10<E, M, H, U>(a, st); \
+    else if (S.variant == 9) launch_update_v9<E, M, H, U>(a, st); \
     else if (S.variant == 5) launch_update_v5<E, M, H, U>(a, st);   \
     else if (S.variant == 4) launch_update_v2<E, M, H, U, true>(a, st); \
     else launch_update_v1<E, M, H, U>(a, st);                  \
@@ -1084,8 +1128,8 @@ extern "C" void pcb200_p2p_export(unsigned char *blob) {
     SYNC_DEVICE();
   }
   cudaIpcMemHandle_t h[3];
-  CK(cudaIpcGetMemHandle(&h[0], S.f[0]));
-  CK(cudaIpcGetMemHandle(&h[1], S.f[1]));
+  CK(cudaIpcGetMemHandle(&h[0], S.f_alloc[0]));
+  CK(cudaIpcGetMemHandle(&h[1], S.f_alloc[1]));
   CK(cudaIpcGetMemHandle(&h[2], S.flags));
   std::memcpy(blob, h, sizeof(h));
 }
@@ -1113,7 +1157,7 @@ extern "C" int pcb200_p2p_connect(const unsigned char *blobs, const int *nranks)
       }
       S.ipc_opened.push_back(p[i]);
     }
-    S.peer_f[d][0] = (double *)p[0]; S.peer_f[d][1] = (double *)p[1]; S.peer_flags[d] = (unsigned long long *)p[2];
+    S.peer_f[d][0] = (double *)p[0] + S.xpad; S.peer_f[d][1] = (double *)p[1] + S.xpad; S.peer_flags[d] = (unsigned long long *)p[2];
   }
   return 0;
 }
@@ -1176,10 +1220,21 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   if (S.initialized) die("initialize_gpu_c called twice");
   check_supported();
   select_device();
+  { // kernel variant (decides the device layout): TMA needs 16-byte global strides -> mx even
+    const bool tma_ok = ((S.cfg.nx + 2 * NG) % 2 == 0);
+    const int kv = S.cfg.kernel_variant;
+    if (kv != 0 && kv != 1 && kv != 4 && kv != 5 && kv != 9 && kv != 10) die("kernel_variant=%d unknown (0 = auto, 1, 4, 5, 9, 10)", kv);
+    if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
+    const bool iso = S.cfg.dx == S.cfg.dy && S.cfg.dy == S.cfg.dz; // variants >= 5 share one set of stencil weights
+    S.variant = kv ? kv : (tma_ok ? (iso ? 10 : 4) : 1);
+    if (S.variant >= 5 && !iso) S.variant = 4; // anisotropic spacing: same kernel structure with per-direction weights
+    S.xpad = S.variant == 10 ? 1 : 0;
+  }
   derive_pars();
   const Pars &P = S.P;
   S.host_f = f;
-  S.nreal = (size_t)P.sv * P.nvar;
+  S.nreal = (size_t)P.mx * P.my * P.mz * P.nvar;
+  S.ndev = (size_t)P.sv * P.nvar + 2;
   // page-lock the Fortran-owned f-array in place (farray_alloc.f90:48-54 allocates it pageable): load_farray_c /
   // copy_farray_c then run as single full-speed DMA transfers without a staging copy.  Already pinned (bench.py) or
   // unpinnable memory is fine -- the copies fall back to the driver's staged path.
@@ -1192,12 +1247,13 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   CK(cudaStreamCreateWithFlags(&S.comm_stream, cudaStreamNonBlocking));
   CK(cudaEventCreateWithFlags(&S.ev_ready, cudaEventDisableTiming));
   CK(cudaEventCreateWithFlags(&S.ev_halo, cudaEventDisableTiming));
-  CK(cudaMalloc(&S.f[0], S.nreal * sizeof(double)));
-  CK(cudaMalloc(&S.f[1], S.nreal * sizeof(double)));
-  CK(cudaMalloc(&S.df, S.nreal * sizeof(double)));
-  CK(cudaMemsetAsync(S.f[0], 0, S.nreal * sizeof(double), S.stream));
-  CK(cudaMemsetAsync(S.f[1], 0, S.nreal * sizeof(double), S.stream));
-  CK(cudaMemsetAsync(S.df, 0, S.nreal * sizeof(double), S.stream));
+  CK(cudaMalloc(&S.f_alloc[0], S.ndev * sizeof(double)));
+  CK(cudaMalloc(&S.f_alloc[1], S.ndev * sizeof(double)));
+  CK(cudaMalloc(&S.df_alloc, S.ndev * sizeof(double)));
+  CK(cudaMemsetAsync(S.f_alloc[0], 0, S.ndev * sizeof(double), S.stream));
+  CK(cudaMemsetAsync(S.f_alloc[1], 0, S.ndev * sizeof(double), S.stream));
+  CK(cudaMemsetAsync(S.df_alloc, 0, S.ndev * sizeof(double), S.stream));
+  S.f[0] = S.f_alloc[0] + S.xpad; S.f[1] = S.f_alloc[1] + S.xpad; S.df = S.df_alloc + S.xpad;
   S.cur = 0;
   CK(cudaMalloc(&S.dt_dev, sizeof(double)));
   CK(cudaMalloc(&S.dt1_dev, sizeof(double)));
@@ -1207,21 +1263,23 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   CK(cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, curdev));
   S.nsm = nsm;
   S.red_blocks = nsm * 8;
-  // kernel variant: TMA needs 16-byte global strides -> mx even
-  const bool tma_ok = (P.mx % 2 == 0);
-  const int kv = S.cfg.kernel_variant;
-  if (kv != 0 && kv != 1 && kv != 4 && kv != 5 && kv != 9) die("kernel_variant=%d unknown (0 = auto, 1, 4, 5, 9)", kv);
-  if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
-  const bool iso = S.cfg.dx == S.cfg.dy && S.cfg.dy == S.cfg.dz; // variant 5 shares one set of stencil weights
-  S.variant = kv ? kv : (tma_ok ? (iso ? 9 : 4) : 1);
-  if (S.variant >= 5 && !iso) S.variant = 4; // anisotropic spacing: same kernel structure with per-direction weights
-  if (S.variant >= 2) make_tensor_map(&S.tmap_df, S.df, V2_TX, V2_TY, P.nvar);
+  if (S.variant >= 2 && S.variant != 10) make_tensor_map(&S.tmap_df, S.df, V2_TX, V2_TY, P.nvar);
   if (S.variant == 4) {
     make_tensor_map(&S.tmap[0], S.f[0]);
     make_tensor_map(&S.tmap[1], S.f[1]);
   }
   if (S.variant == 9) {
     for (int w = 0; w < 2; ++w) make_tensor_map(&S.tmap9[w], S.f[w], V2_HX, V2_HY, P.nvar);
+  }
+  if (S.variant == 10) { // tensor maps over the ALLOCATIONS: x coordinates are physical (logical + 1)
+    for (int w = 0; w < 2; ++w) {
+      make_tensor_map(&S.tmap9[w], S.f_alloc[w], V10_HX, V2_HY, P.nvar);
+      make_tensor_map(&S.tmap10_i[w], S.f_alloc[w], V2_TX, V2_TY, P.nvar);
+      make_tensor_map(&S.tmap10_o1[w], S.f_alloc[w], V2_TX, V2_TY, 1, true);
+      make_tensor_map(&S.tmap10_o3[w], S.f_alloc[w], V2_TX, V2_TY, 3, true);
+    }
+    make_tensor_map(&S.tmap10_d1, S.df_alloc, V2_TX, V2_TY, 1, true);
+    make_tensor_map(&S.tmap10_d3, S.df_alloc, V2_TX, V2_TY, 3, true);
   }
   if (S.variant == 5) {
     for (int w = 0; w < 2; ++w) {
@@ -1280,7 +1338,7 @@ extern "C" void finalize_gpu_c(void) {
   for (void *q : S.ipc_opened) cudaIpcCloseMemHandle(q);
   S.ipc_opened.clear();
   if (S.flags) { cudaFree(S.flags); cudaFree(S.seq_slots); }
-  cudaFree(S.f[0]); cudaFree(S.f[1]); cudaFree(S.df);
+  cudaFree(S.f_alloc[0]); cudaFree(S.f_alloc[1]); cudaFree(S.df_alloc);
   if (S.ybuf) cudaFree(S.ybuf);
   cudaFree(S.dt_dev); cudaFree(S.dt1_dev); cudaFree(S.partial); cudaFree(S.diag_dev); cudaFree(S.fx_dev); cudaFree(S.fpq_dev);
   cudaFreeHost(S.pinned);
@@ -1294,6 +1352,20 @@ extern "C" void finalize_gpu_c(void) {
 }
 FTN_ALIAS(finalize_gpu_c)
 
+// host f-array (rows of mx doubles, contiguous) <-> device buffer (row pitch P.sy): `rows` rows from row `row0`
+static void copy_rows(double *dev, double *host, size_t row0, size_t rows, cudaMemcpyKind kind, cudaStream_t st) {
+  const Pars &P = S.P;
+  double *d = dev + row0 * P.sy, *h = host + row0 * P.mx;
+  if (P.sy == P.mx) {
+    if (kind == cudaMemcpyHostToDevice) CK(cudaMemcpyAsync(d, h, rows * P.mx * sizeof(double), kind, st));
+    else CK(cudaMemcpyAsync(h, d, rows * P.mx * sizeof(double), kind, st));
+  } else if (kind == cudaMemcpyHostToDevice) {
+    CK(cudaMemcpy2DAsync(d, P.sy * sizeof(double), h, P.mx * sizeof(double), P.mx * sizeof(double), rows, kind, st));
+  } else {
+    CK(cudaMemcpy2DAsync(h, P.mx * sizeof(double), d, P.sy * sizeof(double), P.mx * sizeof(double), rows, kind, st));
+  }
+}
+
 extern "C" void load_farray_c(void) {
   need_init("load_farray_c");
   wait_halo(S.stream);
@@ -1302,13 +1374,10 @@ extern "C" void load_farray_c(void) {
     // z is decomposed: the exchange below rewrites the z-ghost planes, and with the peer-put halo a neighbour whose
     // upload finishes earlier may already have written them -- a whole-array copy would overwrite its planes with
     // stale host data after the arrival flag was raised.  Copy the interior planes only (contiguous per variable).
-    const size_t planes = (size_t)S.P.nz * S.P.sz;
-    for (int k = 0; k < S.P.nvar; ++k) {
-      const size_t off = (size_t)k * S.P.sv + (size_t)NG * S.P.sz;
-      CK(cudaMemcpyAsync(S.f[S.cur] + off, S.host_f + off, planes * sizeof(double), cudaMemcpyHostToDevice, S.stream));
-    }
+    for (int k = 0; k < S.P.nvar; ++k)
+      copy_rows(S.f[S.cur], S.host_f, ((size_t)k * S.P.mz + NG) * S.P.my, (size_t)S.P.nz * S.P.my, cudaMemcpyHostToDevice, S.stream);
   } else {
-    CK(cudaMemcpyAsync(S.f[S.cur], S.host_f, S.nreal * sizeof(double), cudaMemcpyHostToDevice, S.stream));
+    copy_rows(S.f[S.cur], S.host_f, 0, (size_t)S.P.my * S.P.mz * S.P.nvar, cudaMemcpyHostToDevice, S.stream);
   }
   update_ghosts(S.f[S.cur], S.stream);
   SYNC_STREAM((S.stream));
@@ -1318,7 +1387,7 @@ FTN_ALIAS(load_farray_c)
 extern "C" void copy_farray_c(double *f) {
   need_init("copy_farray_c");
   wait_halo(S.stream);
-  CK(cudaMemcpyAsync(f, S.f[S.cur], S.nreal * sizeof(double), cudaMemcpyDeviceToHost, S.stream));
+  copy_rows(S.f[S.cur], f, 0, (size_t)S.P.my * S.P.mz * S.P.nvar, cudaMemcpyDeviceToHost, S.stream);
   SYNC_STREAM((S.stream));
 }
 FTN_ALIAS(copy_farray_c)
@@ -1333,14 +1402,14 @@ extern "C" void pcb200_copy_farray_async(double *f) {
     CK(cudaStreamCreateWithFlags(&S.copy_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&S.ev_snap, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&S.ev_d2h, cudaEventDisableTiming));
-    CK(cudaMalloc(&S.snap, S.nreal * sizeof(double)));
+    CK(cudaMalloc(&S.snap, S.ndev * sizeof(double)));
   }
   if (S.d2h_pending) { SYNC_EVENT((S.ev_d2h)); S.d2h_pending = false; }
   wait_halo(S.stream);
-  CK(cudaMemcpyAsync(S.snap, S.f[S.cur], S.nreal * sizeof(double), cudaMemcpyDeviceToDevice, S.stream));
+  CK(cudaMemcpyAsync(S.snap, S.f_alloc[S.cur], S.ndev * sizeof(double), cudaMemcpyDeviceToDevice, S.stream));
   CK(cudaEventRecord(S.ev_snap, S.stream));
   CK(cudaStreamWaitEvent(S.copy_stream, S.ev_snap, 0));
-  CK(cudaMemcpyAsync(f, S.snap, S.nreal * sizeof(double), cudaMemcpyDeviceToHost, S.copy_stream));
+  copy_rows(S.snap + S.xpad, f, 0, (size_t)S.P.my * S.P.mz * S.P.nvar, cudaMemcpyDeviceToHost, S.copy_stream);
   CK(cudaEventRecord(S.ev_d2h, S.copy_stream));
   S.d2h_pending = true;
 }

@@ -33,7 +33,7 @@ def _cfg(name, **over):
     return c
 
 
-VARIANTS = [1, 4, 5, 9]
+VARIANTS = [1, 4, 5, 9, 10]
 
 
 @pytest.mark.parametrize("variant", VARIANTS)
@@ -50,7 +50,7 @@ def test_one_substep(oracle_mod, name, variant):
     assert err.max() <= TOL_SUBSTEP, (name, variant, err)
 
 
-@pytest.mark.parametrize("variant", [4, 5, 9])
+@pytest.mark.parametrize("variant", [4, 5, 9, 10])
 @pytest.mark.parametrize("shape", [(32, 8, 4), (64, 16, 40), (70, 9, 5), (6, 6, 6), (34, 10, 17), (40, 24, 3), (32, 8, 100)])
 def test_tma_variants_tile_edges(oracle_mod, shape, variant):
     """grids that are not multiples of the 32x8 tile, shorter than one tile, the minimum nz = 3, and z-chunk remainders"""
