@@ -207,6 +207,85 @@ def test_full_size_512_independent_kernels_agree_and_ghosts_wrap():
     assert np.array_equal(a[:, :3], a[:, n:n + 3]) and np.array_equal(a[:, n + 3:], a[:, 3:6])
 
 
+
+def test_full_size_512_one_substep_against_the_oracle_on_z_windows(oracle_mod):
+    """BASELINE config[2] at its full size against the ORACLE (not against another CUDA kernel): one substep of the
+    512^3 MHD+entropy run on the device-generated state; the oracle evaluates the RHS on three 16-plane z windows
+    (bottom, middle, top of the box) whose ghost planes are the neighbouring planes of the same host array --
+    pc_oracle_rhs only needs valid ghosts, so a window is an exact sub-problem for one substep."""
+    import torch
+    from pencil_code_b200.gpu import GPU
+    if torch.cuda.mem_get_info()[1] < 60e9:
+        pytest.skip("needs a B200-class device (26.7 GB per instance)")
+    n, w = 512, 16
+    cfg = pcfg.config_mhd_entropy(n)
+    dt = pcfg.fixed_dt(cfg)
+    f0 = np.zeros(synthetic.farray_shape(cfg))
+    g = GPU(cfg)
+    g.initialize_GPU(f0, nt=0)
+    g.init_synthetic(12345)
+    g.copy_farray_from_GPU(f0)  # state before the substep, ghost zones filled
+    g.set_dt(dt, False)
+    g.rhs_GPU(f0, 1)
+    f1 = np.empty_like(f0)
+    g.copy_farray_from_GPU(f1)
+    g.finalize_GPU()
+    wcfg = dict(cfg, nz=w)
+    o = oracle_mod.Oracle(wcfg)
+    beta1 = 1.0 / 3.0
+    for z0 in (3, 3 + n // 2 - w // 2, 3 + n - w):  # first interior plane of the window (array index)
+        fw = np.ascontiguousarray(f0[:, z0 - 3:z0 + w + 3])
+        dfw = np.zeros_like(fw)
+        o.rhs(fw, dfw)
+        ref = fw + dt * beta1 * dfw
+        got = f1[:, z0 - 3:z0 + w + 3]
+        err = pu.rel_linf(np.ascontiguousarray(got), ref)
+        assert err.max() <= TOL_SUBSTEP, (z0, err)
+
+
+@pytest.mark.parametrize("which", ["hydro_hyper3_256", "mhd_entropy_256"])
+def test_configs_at_256_three_steps_against_the_oracle(oracle_mod, which):
+    """BASELINE config[4] (hydro + hyperdiffusion, 256^3) at its full size and config[2]'s physics at 256^3: three
+    forced RK3 steps, whole domain, against the oracle."""
+    cfg = pcfg.config_hydro_hyper3(256) if which == "hydro_hyper3_256" else pcfg.config_mhd_entropy(256)
+    fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 3, dt=pcfg.fixed_dt(cfg), forcing=pcfg.kvectors())
+    assert pu.rel_linf(fg, fc).max() <= 1e-11
+
+
+def test_hyper3_simplified_viscosity(oracle_mod):
+    """ivisc='hyper3-simplified' (viscosity.f90:1982-1989: fvisc += nu_hyper3 del6 u) alone and together with nu-const"""
+    for extra in (dict(lvisc_nu_const=0, nu=0.0), dict(lvisc_nu_const=1, nu=3e-3)):
+        cfg = _cfg("hydro_hyper3", lvisc_hyper3_simplified=1, lvisc_hyper3_nu_const=0, nu_hyper3=1e-6, **extra)
+        fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 0, dt=pcfg.fixed_dt(cfg), substeps_only=1)
+        assert pu.rel_linf(fg, fc).max() <= TOL_SUBSTEP, extra
+        fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 20, dt=pcfg.fixed_dt(cfg))
+        assert pu.rel_linf(fg, fc).max() <= TOL_100, extra
+
+
+@pytest.mark.parametrize("name", ["mhd_entropy_upwind", "ragged"])
+def test_upwind_and_ragged_20_steps(oracle_mod, name):
+    """upwinded advection of u, lnrho, s and the upwinded induction term; odd mx (global-load kernel): 20 steps"""
+    cfg = _cfg(name)
+    fg, fc, sg, sc, _ = pu.run_both(cfg, oracle_mod, 20, dt=pcfg.fixed_dt(cfg), diag_every=5)
+    assert pu.rel_linf(fg, fc).max() <= TOL_100
+    for a, b in zip(sg, sc):
+        for k in ("urms", "brms", "jrms"):
+            assert abs(a[k] - b[k]) <= TOL_100 * abs(b[k])
+
+
+def test_config1_helical_mhd_128_hundred_steps(oracle_mod):
+    """BASELINE config[1] at full size, the north-star's long-run criterion: 100 forced steps, f-array and the
+    urms/brms/dt time series within 1e-9 of the oracle (about 2 minutes of oracle time on 16 cores)."""
+    cfg = pcfg.config_helical_mhd_128()
+    fg, fc, sg, sc, _ = pu.run_both(cfg, oracle_mod, 100, dt=pcfg.fixed_dt(cfg), forcing=pcfg.kvectors(), diag_every=10)
+    err = pu.rel_linf(fg, fc)
+    print("config[1] 128^3, 100 steps: rel Linf per variable", err)
+    assert err.max() <= TOL_100
+    for a, b in zip(sg, sc):
+        for k in ("urms", "brms", "jrms"):
+            assert abs(a[k] - b[k]) <= TOL_100 * abs(b[k])
+
+
 def test_async_copy_is_a_snapshot(tmp_path):
     """pcb200_copy_farray_async: the host array receives the state at the time of the call even though the time loop
     keeps running while the transfer is in flight; written as var.dat it restarts a run bit-identically"""
