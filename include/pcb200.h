@@ -178,6 +178,9 @@ void *pos_real_ptr_c(void **ptr, int *ind);
 void split_update_gpu_c(double *f);
 void radtransfer_gpu_c(void);
 void test_bcs_c(void);
+/* the check behind test_bcs_c (astaroth/gpu_astaroth.cc:2283-2454 testBCs): number of ghost values that differ from the
+   CPU boundary conditions on a randomised mesh by more than 1e-12 relative (0 = passed); does not exit */
+long long pcb200_test_bcs(void);
 
 /* gpu.h:12 n_gpu_reduced_vars=20.  Slot layout of dst[]: */
 enum {

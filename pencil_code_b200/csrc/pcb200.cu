@@ -1516,7 +1516,89 @@ extern "C" void get_gpu_reduced_vars_c(double *dst) {
 }
 FTN_ALIAS(get_gpu_reduced_vars_c)
 
-extern "C" void test_bcs_c(void) { need_init("test_bcs_c"); }
+// testBCs (astaroth/gpu_astaroth.cc:2283-2454; Fortran: ltest_bcs -> test_gpu_bcs): a randomised mesh (same seed) is
+// loaded to the device, the device boundary/halo path fills its ghost zones, and every ghost value of the directions
+// this rank wraps by itself is compared with the CPU boundary conditions applied to the same host mesh (periodic
+// images in x, then y, then z: boundcond.f90:2387-2433) to 1e-12 relative, with the reference's reporting.  The
+// reference returns early for all-periodic set-ups; here the check runs, because the periodic path is the only one.
+// The mesh lives in the idle f buffer (the one the next substep overwrites), so the state of the run is untouched.
+// Returns the number of differing values (pcb200_test_bcs); test_bcs_c exits with EXIT_FAILURE like the reference.
+extern "C" long long pcb200_test_bcs(void) {
+  need_init("pcb200_test_bcs");
+  const Pars &P = S.P;
+  wait_halo(S.stream);
+  SYNC_STREAM((S.stream));
+  const size_t n = S.nreal;
+  std::vector<double> mesh(n), out(n);
+  srand(321654987);
+  for (size_t i = 0; i < n; ++i) mesh[i] = (double)rand() / (double)RAND_MAX; // acHostMeshRandomize
+  double *scratch = S.f[S.cur ^ 1];
+  const size_t rows = (size_t)P.my * P.mz * P.nvar;
+  copy_rows(scratch, mesh.data(), 0, rows, cudaMemcpyHostToDevice, S.stream);
+  update_ghosts(scratch, S.stream);
+  wait_halo(S.stream);
+  copy_rows(scratch, out.data(), 0, rows, cudaMemcpyDeviceToHost, S.stream);
+  SYNC_STREAM((S.stream));
+  // CPU truth on the host mesh: x, then y (incl. x ghosts), then z (incl. both), only in the directions wrapped locally
+  const bool wy = S.cfg.nprocy == 1, wz = S.cfg.nprocz == 1; // (the loopback test hook exchanges with itself: periodic too)
+  auto at = [&](std::vector<double> &a, int k, int iz, int iy, int ix) -> double & {
+    return a[(((size_t)k * P.mz + iz) * P.my + iy) * P.mx + ix];
+  };
+  for (int k = 0; k < P.nvar; ++k) {
+    for (int iz = 0; iz < P.mz; ++iz)
+      for (int iy = 0; iy < P.my; ++iy)
+        for (int g = 0; g < NG; ++g) {
+          at(mesh, k, iz, iy, g) = at(mesh, k, iz, iy, g + P.nx);
+          at(mesh, k, iz, iy, NG + P.nx + g) = at(mesh, k, iz, iy, NG + g);
+        }
+    if (wy)
+      for (int iz = 0; iz < P.mz; ++iz)
+        for (int g = 0; g < NG; ++g)
+          for (int ix = 0; ix < P.mx; ++ix) {
+            at(mesh, k, iz, g, ix) = at(mesh, k, iz, g + P.ny, ix);
+            at(mesh, k, iz, NG + P.ny + g, ix) = at(mesh, k, iz, NG + g, ix);
+          }
+    if (wz)
+      for (int g = 0; g < NG; ++g)
+        for (int iy = 0; iy < P.my; ++iy)
+          for (int ix = 0; ix < P.mx; ++ix) {
+            at(mesh, k, g, iy, ix) = at(mesh, k, g + P.nz, iy, ix);
+            at(mesh, k, NG + P.nz + g, iy, ix) = at(mesh, k, NG + g, iy, ix);
+          }
+  }
+  // comparison region: interior extents in the directions this rank does not wrap (their ghosts come from neighbours)
+  const int y0 = wy ? 0 : NG, y1 = wy ? P.my : NG + P.ny, z0 = wz ? 0 : NG, z1 = wz ? P.mz : NG + P.nz;
+  const double eps = 1e-12;
+  long long bad = 0, points = 0;
+  double max_rel = -1.0, gpu_val = 0.0, true_val_l = 0.0;
+  int where[4] = {0, 0, 0, 0};
+  for (int k = 0; k < P.nvar; ++k)
+    for (int iz = z0; iz < z1; ++iz)
+      for (int iy = y0; iy < y1; ++iy)
+        for (int ix = 0; ix < P.mx; ++ix) {
+          const bool in = ix >= NG && ix < NG + P.nx && iy >= NG && iy < NG + P.ny && iz >= NG && iz < NG + P.nz;
+          if (in) continue;
+          ++points;
+          const double o = at(out, k, iz, iy, ix), t = at(mesh, k, iz, iy, ix), d = std::fabs(o - t);
+          if (std::fabs(d / t) > eps || (t == 0.0 && std::fabs(o) > 1e-13) || std::isnan(o)) {
+            ++bad;
+            if (t != 0.0 && d / std::fabs(t) > max_rel) { max_rel = d / std::fabs(t); gpu_val = o; true_val_l = t; where[0] = ix; where[1] = iy; where[2] = iz; where[3] = k; }
+          }
+        }
+  if (bad) {
+    std::fprintf(stderr, "ratio of values wrong: %f\n", (double)bad / (double)points);
+    std::fprintf(stderr, "max abs relative difference val: %.7e\n", max_rel);
+    std::fprintf(stderr, "Point where biggest rel diff: %d,%d,%d in Field: %d\n", where[0], where[1], where[2], where[3]);
+    std::fprintf(stderr, "largest difference: %.7e\t%.7e\n", gpu_val, true_val_l);
+    std::fprintf(stderr, "Did not pass BC test :(\n");
+  } else {
+    std::fprintf(stderr, "Passed BC test :)\n");
+  }
+  return bad;
+}
+extern "C" void test_bcs_c(void) {
+  if (pcb200_test_bcs() != 0) std::exit(EXIT_FAILURE);
+}
 FTN_ALIAS(test_bcs_c)
 
 // updateInConfig* (gpu_astaroth.cc:2179-2241): run-time parameter pushes by name

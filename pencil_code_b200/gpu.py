@@ -68,7 +68,7 @@ ABI_SYMBOLS = (
     "get_farray_ptr_gpu_c", "reload_gpu_config_c", "update_on_gpu_scal_by_name_c", "update_on_gpu_vec_by_name_c",
     "update_on_gpu_arr_by_name_c", "update_on_gpu_scal_by_ind_c", "update_on_gpu_vec_by_ind_c",
     "update_on_gpu_arr_by_ind_c", "pos_real_ptr_c", "split_update_gpu_c", "radtransfer_gpu_c", "test_bcs_c",
-    "get_gpu_reduced_vars_c", "pcb200_driver_run",
+    "get_gpu_reduced_vars_c", "pcb200_driver_run", "pcb200_test_bcs",
 )
 # the reference binds these with a trailing underscore (FTNIZE, src/headers_c.h:31-37)
 FTN_SYMBOLS = tuple(s + "_" for s in ABI_SYMBOLS if s.endswith("_c"))
@@ -123,6 +123,10 @@ def load_library():
     L.split_update_gpu_c.argtypes = [dp]
     L.pcb200_driver_run.argtypes = [C.POINTER(DriverState), C.c_int, dp, C.c_int]
     L.pcb200_driver_run.restype = C.c_int
+    L.pcb200_test_bcs.restype = C.c_longlong
+    L.pcb200_reconfigure.argtypes = [C.POINTER(Config)]
+    L.pos_real_ptr_c.argtypes = [C.POINTER(C.c_void_p), ip]
+    L.pos_real_ptr_c.restype = C.c_void_p
     if L.pcb200_sizeof_config() != C.sizeof(Config):
         raise RuntimeError("pcb200_config layout mismatch between gpu.py and libpcb200.so")
     _lib = L
@@ -238,6 +242,8 @@ class GPU:
         idx = self.L.update_on_gpu_scal_by_name_c(varname.encode() + b"\0", C.byref(v))
         if idx < 0:
             raise KeyError('update_on_gpu: variable "%s" not found' % varname)
+        if varname in self.cfg:
+            self.cfg[varname] = value  # a later reconfigure() sends the complete struct
         return idx
 
     def get_gpu_reduced_vars(self):
@@ -249,7 +255,49 @@ class GPU:
         self.L.split_update_gpu_c(_dp(f))
 
     def test_gpu_bcs(self):
+        """ltest_bcs (gpu_astaroth.f90 test_gpu_bcs): exits the process with EXIT_FAILURE when the check fails"""
         self.L.test_bcs_c()
+
+    def test_bcs_count(self):
+        """number of ghost values that differ from the CPU boundary conditions (0 = passed); never exits"""
+        return int(self.L.pcb200_test_bcs())
+
+    def reconfigure(self, **changes):
+        """RELOAD path of gpu_b200.f90: new physics parameters while initialized (pcb200_reconfigure + reload)"""
+        self.cfg.update(changes)
+        self._c = make_struct(self.cfg)
+        self.L.pcb200_reconfigure(C.byref(self._c))
+        self.L.reload_gpu_config_c()
+
+    def pos_real_ptr(self, base, ind):
+        b = C.c_void_p(base)
+        return self.L.pos_real_ptr_c(C.byref(b), C.byref(C.c_int(ind)))
+
+    def driver_run(self, nt, dt, ldt=False, t=0.0, it=0, forcing=None, it1=0, seed=2024):
+        """pcb200_driver_run: the C++ mirror of run.f90/timestep.f90's loop (forcing: HelicalForcing or None).
+        Returns (t, dt, it, rows) with rows = [(it, t, {reduced vars})] of the it1-th steps."""
+        st = DriverState()
+        st.t, st.dt, st.it, st.ldt = t, dt, it, int(ldt)
+        st.lforcing = 0 if forcing is None else 1
+        st.it1 = it1
+        keep = None
+        if forcing is not None:
+            n = len(forcing.kvecs)
+            arr = [(C.c_double * n)(*[k[i] for k in forcing.kvecs]) for i in range(3)]
+            keep = arr
+            st.force, st.relhel, st.kav, st.nk = forcing.force, forcing.relhel, forcing.kav, n
+            st.kkx, st.kky, st.kkz = [C.cast(a, C.POINTER(C.c_double)) for a in arr]
+            st.rng_state = seed & 0xFFFFFFFFFFFFFFFF
+        rowlen = N_GPU_REDUCED_VARS + 2
+        max_rows = nt + 1
+        buf = (C.c_double * (rowlen * max_rows))()
+        nrows = self.L.pcb200_driver_run(C.byref(st), nt, buf, max_rows)
+        rows = []
+        for r in range(nrows):
+            v = buf[r * rowlen:(r + 1) * rowlen]
+            rows.append((int(v[0]), v[1], dict(zip(REDUCED_NAMES, v[2:]))))
+        del keep
+        return st.t, st.dt, st.it, rows
 
     def get_farray_ptr_gpu(self):
         a, b = C.c_void_p(), C.c_void_p()
