@@ -52,6 +52,7 @@ static long long g_host_syncs = 0; // blocking host synchronisations issued by t
 struct UpdateArgs {
   const double *fin;
   double *fout;
+  int z_lo2 = 0, z_hi2 = 0; // optional second z range (variant 10 serves both in one launch)
   double *df;
   const double *dt_dev; // dt of this step (device resident)
   double alpha, beta;
@@ -677,7 +678,9 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v10(
     }
   }
   v.lz = (nzr + pick - 1) / pick;
-  const int nch = (nzr + v.lz - 1) / v.lz;
+  int nch = (nzr + v.lz - 1) / v.lz;
+  v.nch1 = nch; v.z_lo2 = a.z_lo2; v.z_hi2 = a.z_hi2;
+  if (a.z_hi2 > a.z_lo2) nch += (a.z_hi2 - a.z_lo2 + v.lz - 1) / v.lz;
   dim3 g(gx, gy, nch), b(V2_TX, V10_CTA / V2_TX, 1); // eight compute warps (+ the producer warpgroup)
   const int w = (a.fin == S.f[0]) ? 0 : 1;
   V10Maps tm;
@@ -1490,9 +1493,15 @@ extern "C" void rhs_gpu_c(int *isubstep, double *t) {
     launch_update(a, st);
     wait_halo(st);
     a.z_lo = NG; a.z_hi = 2 * NG;                 // bottom 3 planes
-    launch_update(a, st);
-    a.z_lo = S.P.nz; a.z_hi = NG + S.P.nz;        // top 3 planes
-    launch_update(a, st);
+    if (S.variant == 10) {                        // ... and the top 3 planes in the same launch
+      a.z_lo2 = S.P.nz; a.z_hi2 = NG + S.P.nz;
+      launch_update(a, st);
+      a.z_lo2 = a.z_hi2 = 0;
+    } else {
+      launch_update(a, st);
+      a.z_lo = S.P.nz; a.z_hi = NG + S.P.nz;      // top 3 planes
+      launch_update(a, st);
+    }
     S.cur ^= 1;
     update_ghosts_xy(S.f[S.cur], st);
     start_z_halo(S.f[S.cur], st);                 // overlaps the next substep's interior kernel

@@ -58,6 +58,7 @@ struct V10Args {
   double alpha, beta;
   int read_df, write_df;
   int z_lo, z_hi, lz;
+  int nch1, z_lo2, z_hi2; // a second z range served by the chunks blockIdx.z >= nch1 (the two boundary slabs of a z-decomposed run in one launch)
   Forcing frc;
 };
 
@@ -113,8 +114,9 @@ __global__ void __launch_bounds__(V10_CTA, 1) rhs_update_v10(const __grid_consta
 
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * V2_TX + tx;
   const int bx0 = blockIdx.x * V2_TX, by0 = blockIdx.y * V2_TY; // origin of the halo'd tile (incl. ghosts)
-  const int zc0 = a.z_lo + blockIdx.z * a.lz;
-  const int zc1 = min(zc0 + a.lz, a.z_hi);
+  const bool second = (int)blockIdx.z >= a.nch1;
+  const int zc0 = second ? a.z_lo2 + ((int)blockIdx.z - a.nch1) * a.lz : a.z_lo + (int)blockIdx.z * a.lz;
+  const int zc1 = min(zc0 + a.lz, second ? a.z_hi2 : a.z_hi);
   if (zc0 >= zc1) return;
   const int nst = (zc1 - zc0) + 2 * NG; // stages: centre planes zc0-3 .. zc1+2
   const int ix = bx0 + tx + NG, iy = by0 + ty + NG;
