@@ -53,6 +53,8 @@ struct UpdateArgs {
   const double *fin;
   double *fout;
   int z_lo2 = 0, z_hi2 = 0; // optional second z range (variant 10 serves both in one launch)
+  const unsigned long long *halo_flags = nullptr; // variant 10, peer-put halo: wait for the neighbours' planes inside the kernel
+  unsigned long long halo_seq = 0;
   double *df;
   const double *dt_dev; // dt of this step (device resident)
   double alpha, beta;
@@ -677,9 +679,11 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v10(
       if (eff > best + 0.01) { best = eff; pick = c; }
     }
   }
+  if (a.halo_flags) pick = std::max(pick, 2); // top-down chunks: the lowest one must not be the first to run
   v.lz = (nzr + pick - 1) / pick;
   int nch = (nzr + v.lz - 1) / v.lz;
   v.nch1 = nch; v.z_lo2 = a.z_lo2; v.z_hi2 = a.z_hi2;
+  v.halo_flags = a.halo_flags; v.halo_seq = a.halo_seq; v.nch = nch;
   if (a.z_hi2 > a.z_lo2) nch += (a.z_hi2 - a.z_lo2 + v.lz - 1) / v.lz;
   dim3 g(gx, gy, nch), b(V2_TX, V10_CTA / V2_TX, 1); // eight compute warps (+ the producer warpgroup)
   const int w = (a.fin == S.f[0]) ? 0 : 1;
@@ -1486,6 +1490,19 @@ extern "C" void rhs_gpu_c(int *isubstep, double *t) {
     launch_update(a, st);
     S.cur ^= 1;
     update_ghosts(S.f[S.cur], st);
+  } else if (S.variant == 10 && S.p2p && S.halo_pending && !std::getenv("PCB200_SPLIT_LAUNCH")) {
+    // peer-put halo: one launch over all planes; the CTAs that read ghost planes wait for the neighbours' arrival
+    // counters themselves (pcb200_v10.cuh: halo_wait), so no boundary launches and no host-side wait in between
+    a.z_lo = NG;
+    a.z_hi = NG + S.P.nz;
+    a.halo_flags = S.flags;
+    a.halo_seq = S.seq;
+    launch_update(a, st);
+    CK(cudaStreamWaitEvent(st, S.ev_halo, 0)); // my own puts have left (they read f[cur], which the next-but-one substep overwrites)
+    S.halo_pending = false;
+    S.cur ^= 1;
+    update_ghosts_xy(S.f[S.cur], st);
+    start_z_halo(S.f[S.cur], st);
   } else {
     // interior planes need no z halo: they run while the exchange of f[cur] is still in flight
     a.z_lo = 2 * NG;

@@ -59,6 +59,12 @@ struct V10Args {
   int read_df, write_df;
   int z_lo, z_hi, lz;
   int nch1, z_lo2, z_hi2; // a second z range served by the chunks blockIdx.z >= nch1 (the two boundary slabs of a z-decomposed run in one launch)
+  // z-decomposed runs with the peer-put halo: ONE launch over all planes; the chunks run top-down (blockIdx.z = 0 is the
+  // uppermost), and a CTA waits for the arrival counter of a neighbour (pcb200.cu: put_z) only when it is about to read
+  // that neighbour's ghost planes -- the lowest chunks start when most of the kernel is done, the halo landed long before
+  const unsigned long long *halo_flags; // [0]: from the lower neighbour (planes < NG), [1]: from the upper one; nullptr: no waits
+  unsigned long long halo_seq;
+  int nch;
   Forcing frc;
 };
 
@@ -115,7 +121,8 @@ __global__ void __launch_bounds__(V10_CTA, 1) rhs_update_v10(const __grid_consta
   const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * V2_TX + tx;
   const int bx0 = blockIdx.x * V2_TX, by0 = blockIdx.y * V2_TY; // origin of the halo'd tile (incl. ghosts)
   const bool second = (int)blockIdx.z >= a.nch1;
-  const int zc0 = second ? a.z_lo2 + ((int)blockIdx.z - a.nch1) * a.lz : a.z_lo + (int)blockIdx.z * a.lz;
+  const int chunk = a.halo_flags ? a.nch - 1 - (int)blockIdx.z : (int)blockIdx.z; // top-down when the halo is awaited in the kernel
+  const int zc0 = second ? a.z_lo2 + ((int)blockIdx.z - a.nch1) * a.lz : a.z_lo + chunk * a.lz;
   const int zc1 = min(zc0 + a.lz, second ? a.z_hi2 : a.z_hi);
   if (zc0 >= zc1) return;
   const int nst = (zc1 - zc0) + 2 * NG; // stages: centre planes zc0-3 .. zc1+2
@@ -138,14 +145,26 @@ __global__ void __launch_bounds__(V10_CTA, 1) rhs_update_v10(const __grid_consta
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
   // ---- producer side (first lane of the ninth warp) -----------------------------------------------------------
+  auto halo_wait = [&](int plane) { // ghost planes of a z neighbour: wait until its put of this exchange has landed
+    if (!a.halo_flags) return;
+    const int d = plane < NG ? 0 : (plane >= NG + P.nz ? 1 : -1);
+    if (d < 0) return;
+    unsigned long long v;
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a.halo_flags + d) : "memory");
+    } while (v < a.halo_seq);
+    asm volatile("fence.proxy.async;" ::: "memory"); // the planes were written by a copy engine: order the TMA reads behind the flag
+  };
   auto load_h = [&](int j) { // halo'd box of the centre plane of stage j
     if (j >= nst) return;
+    halo_wait(zc0 - NG + j);
     const int sh = j % V10_NH;
     mbar_expect_tx(&hbar[sh], L::HTX);
     tma_load_4d(hring + sh * L::HSLOT, &tm.h, &hbar[sh], bx0, by0, zc0 - NG + j, 0);
   };
   auto load_i = [&](int j) { // interior box of plane centre + 3 of stage j
     if (j >= nst) return;
+    halo_wait(zc0 + j);
     const int si = j % V10_NI;
     mbar_expect_tx(&ibar[si], L::ITX);
     tma_load_4d(iring + si * L::ISLOT, &tm.i, &ibar[si], bx0 + NG + 1, by0 + NG, zc0 + j, 0);
@@ -242,13 +261,19 @@ __global__ void __launch_bounds__(V10_CTA, 1) rhs_update_v10(const __grid_consta
   const int toff = (ty + NG) * V10_HX + (tx + NG + 1);
   const long long sv = P.sv, sz = P.sz;
   const long long col = ixc + P.sy * iyc;
+  if (a.halo_flags && zc0 - NG < NG) { // the history loads below read the lower neighbour's planes
+    unsigned long long v;
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(a.halo_flags) : "memory");
+    } while (v < a.halo_seq);
+  }
   { // z histories of the first evaluated plane zc0: own column, planes zc0-3..zc0+2 (coalesced global loads)
     const double *g = a.fin + col + sz * (zc0 - NG);
 #pragma unroll
     for (int k = 0; k < NV; ++k) {
       double h[6];
 #pragma unroll
-      for (int d = 0; d < 6; ++d) h[d] = __ldg(g + k * sv + sz * d);
+      for (int d = 0; d < 6; ++d) h[d] = a.halo_flags ? __ldcg(g + k * sv + sz * d) : __ldg(g + k * sv + sz * d);
       t9_st4(tmh + 12u * k, h[0], h[1], h[2], h[3]);
       t9_st2(tmh + 12u * k + 8u, h[4], h[5]);
     }
