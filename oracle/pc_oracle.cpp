@@ -143,7 +143,7 @@ struct Pencil {
   V lnrho, rho, rho1, glnrho, uglnrho, sglnrho, del2lnrho, del6lnrho, uij5glnrho;
   V ss, gss, del2ss, cs2, lnTT, TT1, glnTT, del2lnTT;
   V ugss, fpres, advec_cs2;
-  V fvisc, visc_heat, diffus_nu, diffus_nu3;
+  V fvisc, visc_heat, diffus_nu, diffus_nu3, diffus_chi;
   V aa, aij, bb, b2, uxb, bij, del2a, jj, j2, jxb, jxbr, ab, jb, ou;
   V advec_uu, advec_va2;
   V tmp, tmp2;
@@ -155,7 +155,7 @@ struct Pencil {
     s(del2lnrho, 1); s(del6lnrho, 1); s(uij5glnrho, 3);
     s(ss, 1); s(gss, 3); s(del2ss, 1); s(cs2, 1); s(lnTT, 1); s(TT1, 1); s(glnTT, 3); s(del2lnTT, 1);
     s(ugss, 1); s(fpres, 3); s(advec_cs2, 1);
-    s(fvisc, 3); s(visc_heat, 1); s(diffus_nu, 1); s(diffus_nu3, 1);
+    s(fvisc, 3); s(visc_heat, 1); s(diffus_nu, 1); s(diffus_nu3, 1); s(diffus_chi, 1);
     s(aa, 3); s(aij, 9); s(bb, 3); s(b2, 1); s(uxb, 3); s(bij, 9); s(del2a, 3); s(jj, 3); s(j2, 1);
     s(jxb, 3); s(jxbr, 3); s(ab, 1); s(jb, 1); s(ou, 1);
     s(advec_uu, 1); s(advec_va2, 1); s(tmp, 1); s(tmp2, 1);
@@ -268,11 +268,38 @@ inline void u_dot_grad_scl(const Deriv &D, int k, const double *gradf, const dou
   if (upwind) doupwind(D, k, uu, ugradf, 0, nx);
 }
 
+// step, der_step sub.f90:4957-5015
+inline double step_fn(double x, double x0, double width) { return 0.5 * (1 + std::tanh((x - x0) / width)); }
+inline double der_step_fn(double x, double x0, double width) {
+  const double arg = std::fabs((x - x0) / width);
+  if (arg >= 8.) return 2. / width * std::exp(-2. * arg);
+  return 0.5 / (width * std::cosh(arg) * std::cosh(arg));
+}
+
 struct Ctx {
   const pc_oracle_pars &P;
   Grid g;
   Eos eos;
-  explicit Ctx(const pc_oracle_pars &p) : P(p), g(p), eos(p) {}
+  V hcond_prof, dlnhcond_prof, profz_cool; // per interior z plane (entropy.f90:7741-7769, 1323+1367)
+  explicit Ctx(const pc_oracle_pars &p) : P(p), g(p), eos(p) {
+    if (p.lheatc_Kprof) {
+      hcond_prof.resize(p.nz); dlnhcond_prof.resize(p.nz);
+      for (int n = 0; n < p.nz; ++n) {
+        const double z = p.z0 + n * p.dz;
+        double h = 1. + (p.hcond1 - 1.) * step_fn(z, p.z1, -p.widthss) + (p.hcond2 - 1.) * step_fn(z, p.z2, p.widthss);
+        dlnhcond_prof[n] = ((p.hcond1 - 1.) * der_step_fn(z, p.z1, -p.widthss) + (p.hcond2 - 1.) * der_step_fn(z, p.z2, p.widthss)) / h;
+        hcond_prof[n] = p.hcond0 * h;
+      }
+    }
+    if (p.cool != 0.0) {
+      profz_cool.resize(p.nz);
+      for (int n = 0; n < p.nz; ++n) {
+        const double z = p.z0 + n * p.dz;
+        const double q = (p.ztop - z) / p.wcool;
+        profz_cool[n] = p.cool * std::exp(-0.5 * (q * q)); // cooling_profile='gaussian' (entropy.f90:1323,1367)
+      }
+    }
+  }
   bool lhydro() const { return P.iux >= 0; }
   bool ldensity() const { return P.ilnrho >= 0; }
   bool lentropy() const { return P.iss >= 0; }
@@ -368,7 +395,7 @@ void calc_pencils_density(const Ctx &c, const Deriv &D, Pencil &p) {
   for (int i = 0; i < nx; ++i) p.rho[i] = std::exp(r[i]);   // rho=exp(lnrho)
   grad(D, il, p.glnrho.data(), nx);
   u_dot_grad_scl(D, il, p.glnrho.data(), p.uu.data(), p.uglnrho.data(), c.P.lupw_lnrho != 0, nx);
-  if (c.lentropy() && c.P.lheatc_chiconst) del2(D, il, p.del2lnrho.data(), nx, p.tmp, p.tmp2);
+  if (c.lentropy() && (c.P.lheatc_chiconst || c.P.lheatc_Kprof)) del2(D, il, p.del2lnrho.data(), nx, p.tmp, p.tmp2);
   if (c.P.ldiff_hyper3lnrho) del6(D, il, p.del6lnrho.data(), nx, p.tmp, p.tmp2);
   multmv_mn(nx, p.sij.data(), p.glnrho.data(), p.sglnrho.data());
   if (c.P.lvisc_hyper3_nu_const) multmv_mn(nx, p.uij5.data(), p.glnrho.data(), p.uij5glnrho.data());
@@ -382,13 +409,13 @@ void calc_pencils_eos(const Ctx &c, const Deriv &D, Pencil &p) {
     const double *r = D.row(c.P.iss, 0, 0);
     for (int i = 0; i < nx; ++i) p.ss[i] = r[i];
     grad(D, c.P.iss, p.gss.data(), nx);
-    if (c.P.lheatc_chiconst) del2(D, c.P.iss, p.del2ss.data(), nx, p.tmp, p.tmp2);
+    if (c.P.lheatc_chiconst || c.P.lheatc_Kprof) del2(D, c.P.iss, p.del2ss.data(), nx, p.tmp, p.tmp2);
     for (int i = 0; i < nx; ++i) p.cs2[i] = e.cs20 * std::exp(e.cv1 * p.ss[i] + e.gamma_m1 * (p.lnrho[i] - e.lnrho0));
     for (int i = 0; i < nx; ++i) p.lnTT[i] = e.lnTT0 + e.cv1 * p.ss[i] + e.gamma_m1 * (p.lnrho[i] - e.lnrho0);
     for (int i = 0; i < nx; ++i) p.TT1[i] = std::exp(-p.lnTT[i]);
     for (int j = 0; j < 3; ++j)
       for (int i = 0; i < nx; ++i) p.glnTT[j * nx + i] = e.gamma_m1 * p.glnrho[j * nx + i] + e.cv1 * p.gss[j * nx + i];
-    if (c.P.lheatc_chiconst)
+    if (c.P.lheatc_chiconst || c.P.lheatc_Kprof)
       for (int i = 0; i < nx; ++i) p.del2lnTT[i] = e.gamma_m1 * p.del2lnrho[i] + e.cv1 * p.del2ss[i];
   } else {
     // eos_idealgas.f90:969-1000 (ilnrho_cs2, isothermal): cs2=cs20
@@ -523,6 +550,13 @@ void calc_all_rhs(const Ctx &c, const Deriv &D, Pencil &p, Cfl &cfl, double *df,
     double *d = dfrow(c.P.iux + j);
     for (int i = 0; i < nx; ++i) d[i] = d[i] - p.ugu[j * nx + i];
   }
+  // coriolis_cartesian hydro.f90:6339-6366 (theta=0): c2=2*Omega
+  if (c.P.Omega != 0.0) {
+    const double c2 = 2 * c.P.Omega;
+    double *dx_ = dfrow(c.P.iux), *dy_ = dfrow(c.P.iux + 1);
+    for (int i = 0; i < nx; ++i) dx_[i] = dx_[i] + c2 * p.uu[nx + i];
+    for (int i = 0; i < nx; ++i) dy_[i] = dy_[i] - c2 * p.uu[i];
+  }
   // calc_viscous_force viscosity.f90:2791-2825: df_u += fvisc
   for (int j = 0; j < 3; ++j) {
     double *d = dfrow(c.P.iux + j);
@@ -556,6 +590,21 @@ void calc_all_rhs(const Ctx &c, const Deriv &D, Pencil &p, Cfl &cfl, double *df,
     // calc_viscous_heat viscosity.f90:2743-2789: df_ss += TT1*visc_heat
     if (c.P.lviscosity_heat)
       for (int i = 0; i < nx; ++i) d[i] = d[i] + p.TT1[i] * p.visc_heat[i];
+    std::fill(p.diffus_chi.begin(), p.diffus_chi.end(), 0.0); // entropy.f90:3789
+    // calc_heatcond (K-profile) entropy.f90:5913-6151: thdiff = rho1*hcond*(del2lnTT + glnTT.(glnTT+glhc))
+    if (c.P.lheatc_Kprof) {
+      const int nz_ = D.n - NG;
+      const double hcond = c.hcond_prof[nz_], glhc3 = c.dlnhcond_prof[nz_];
+      V glnThcond((size_t)3 * nx), g2(nx);
+      for (int k = 0; k < 3 * nx; ++k) glnThcond[k] = p.glnTT[k] + (k >= 2 * nx ? glhc3 : 0.);
+      dot_mn(nx, p.glnTT.data(), glnThcond.data(), g2.data());
+      for (int i = 0; i < nx; ++i) {
+        const double thdiff = p.rho1[i] * hcond * (p.del2lnTT[i] + g2[i]);
+        const double chix = p.rho1[i] * hcond * c.eos.cv1;
+        d[i] = d[i] + thdiff;
+        if (lcourant) p.diffus_chi[i] = p.diffus_chi[i] + chix * g.dxyz_2;
+      }
+    }
     // calc_heatcond_constchi entropy.f90:4852-4947
     if (c.P.lheatc_chiconst) {
       V gsum((size_t)3 * nx), g2(nx);
@@ -564,7 +613,19 @@ void calc_all_rhs(const Ctx &c, const Deriv &D, Pencil &p, Cfl &cfl, double *df,
       const double cp = 1 / c.eos.cp1; // p%cp=1/cp1 eos_idealgas.f90:811
       for (int i = 0; i < nx; ++i) d[i] = d[i] + c.P.chi * cp * (p.del2lnTT[i] + g2[i]);
       if (lcourant)
-        for (int i = 0; i < nx; ++i) cfl.maxdiffus[i] = std::max(cfl.maxdiffus[i], (c.eos.gamma * c.P.chi) * g.dxyz_2);
+        for (int i = 0; i < nx; ++i) p.diffus_chi[i] = p.diffus_chi[i] + (c.eos.gamma * c.P.chi) * g.dxyz_2;
+    }
+    if (lcourant) // entropy.f90:3826-3829
+      for (int i = 0; i < nx; ++i) cfl.maxdiffus[i] = std::max(cfl.maxdiffus[i], p.diffus_chi[i]);
+    // calc_heat_cool entropy.f90:6387-6598 with get_heat_cool_gravz :6761-6828 (cooling_profile='gaussian',
+    // lcooling_to_cs2cool=T, luminosity=0): heat = -profz_cool(n)*(cs2-cs2cool)/cs2cool ; df_ss += TT1*rho1*heat
+    if (c.P.cool != 0.0) {
+      const double pc = c.profz_cool[D.n - NG];
+      for (int i = 0; i < nx; ++i) {
+        double heat = 0.0;
+        heat = heat - pc * (p.cs2[i] - c.P.cs2cool) / c.P.cs2cool;
+        d[i] = d[i] + p.TT1[i] * p.rho1[i] * heat;
+      }
     }
   }
   if (lcourant)
@@ -608,11 +669,16 @@ void calc_all_rhs(const Ctx &c, const Deriv &D, Pencil &p, Cfl &cfl, double *df,
     if (lcourant) // :6541-6573 diffus_eta=eta*dxyz_2
       for (int i = 0; i < nx; ++i) cfl.maxdiffus[i] = std::max(cfl.maxdiffus[i], c.P.eta * g.dxyz_2);
   }
+  // addgravity gravity_simple.f90:1083-1162 (equ.f90:1316): df_uz += gravz_zpencil(n), profile 'const'
+  if (c.P.gravz != 0.0) {
+    double *d = dfrow(c.P.iux + 2);
+    for (int i = 0; i < nx; ++i) d[i] = d[i] + c.P.gravz;
+  }
 }
 
 struct Accum { // per-thread diagnostic accumulators
   double dt1 = 0, u2s = 0, u2m = 0, rhos = 0, b2s = 0, b2m = 0, j2s = 0, j2m = 0, abs_ = 0, jbs = 0, ous = 0,
-         epsKs = 0, sss = 0, dtu = 0, dtc = 0, dtb = 0, dtnu = 0;
+         epsKs = 0, sss = 0, dtu = 0, dtc = 0, dtb = 0, dtnu = 0, dtchi = 0;
 };
 
 } // namespace
@@ -640,13 +706,69 @@ void pc_oracle_update_ghosts(const pc_oracle_pars *P, double *f) {
           f[g.idx(ix, NG + g.ny + q, iz, k)] = f[g.idx(ix, NG + q, iz, k)];
         }
     // z
-    for (int q = 0; q < NG; ++q)
+    if (P->bcz[0][k] == PC_BC_P)
+      for (int q = 0; q < NG; ++q)
+        for (int iy = 0; iy < g.my; ++iy)
+          for (int ix = 0; ix < g.mx; ++ix) {
+            f[g.idx(ix, iy, q, k)] = f[g.idx(ix, iy, g.nz + q, k)];
+            f[g.idx(ix, iy, NG + g.nz + q, k)] = f[g.idx(ix, iy, NG + q, k)];
+          }
+  }
+  // non-periodic z: boundconds_z boundcond.f90:1421-1787 -- bottom for all variables in slot order, then top; every
+  // condition acts on whole (mx,my) planes, x/y ghosts included
+  Eos e(*P);
+  const int n1 = NG, n2 = NG + g.nz - 1;
+  for (int tb = 0; tb < 2; ++tb)
+    for (int k = 0; k < P->nvar; ++k) {
+      const int bc = P->bcz[tb][k];
+      if (bc == PC_BC_P) continue;
+      const int nb = tb == 0 ? n1 : n2, dir = tb == 0 ? +1 : -1; // ghost plane nb - dir*i mirrors nb + dir*i
       for (int iy = 0; iy < g.my; ++iy)
         for (int ix = 0; ix < g.mx; ++ix) {
-          f[g.idx(ix, iy, q, k)] = f[g.idx(ix, iy, g.nz + q, k)];
-          f[g.idx(ix, iy, NG + g.nz + q, k)] = f[g.idx(ix, iy, NG + q, k)];
+          auto F = [&](int iz, int kk) -> double & { return f[g.idx(ix, iy, iz, kk)]; };
+          switch (bc) {
+          case PC_BC_S: // bc_sym_z sgn=+1 :3842-3900
+            for (int i = 1; i <= NG; ++i) F(nb - dir * i, k) = F(nb + dir * i, k);
+            break;
+          case PC_BC_A: // sgn=-1: antisymmetry, boundary value 0
+            for (int i = 1; i <= NG; ++i) F(nb - dir * i, k) = -F(nb + dir * i, k);
+            F(nb, k) = 0.;
+            break;
+          case PC_BC_A2: // sgn=-1, rel=T: bottom 2*f(n1)+sgn*f(n1+i) ; top f(n2)+(f(n2)+sgn*f(n2-i))
+            for (int i = 1; i <= NG; ++i) {
+              if (tb == 0) F(nb - i, k) = 2 * F(nb, k) - F(nb + i, k);
+              else F(nb + i, k) = F(nb, k) + (F(nb, k) - F(nb - i, k));
+            }
+            break;
+          case PC_BC_C1: { // bc_ss_flux entropy_bcs.f90:93-235 (not lheatc_chiconst, not Kramers)
+            if (k != P->iss || P->lheatc_chiconst) { std::fprintf(stderr, "pc_oracle: bcz 'c1' only for ss with K-profile conduction\n"); std::exit(1); }
+            const int il = P->ilnrho;
+            double cs2_xy = F(nb, k);
+            cs2_xy = e.cs20 * std::exp(e.gamma_m1 * (F(nb, il) - e.lnrho0) + e.cv1 * cs2_xy);
+            const double tmp_xy = e.cp * (tb == 0 ? P->FbotKbot : P->FtopKtop) / cs2_xy;
+            for (int i = 1; i <= NG; ++i) {
+              const double dz2_bound = 2. * (i * P->dz); // grid.f90:3149-3151
+              if (tb == 0) {
+                const double dlnrho = F(nb + i, il) - F(nb - i, il); // getdlnrho_z density_methods.f90:409-426
+                F(nb - i, k) = F(nb + i, k) + (e.cp - e.cv) * (dlnrho + dz2_bound * tmp_xy);
+              } else {
+                const double dlnrho = F(nb + i, il) - F(nb - i, il);
+                F(nb + i, k) = F(nb - i, k) + (e.cp - e.cv) * (-dlnrho - dz2_bound * tmp_xy);
+              }
+            }
+          } break;
+          case PC_BC_CT: { // bc_ss_temp_z eos_idealgas.f90:3112-3260 (entropy, logarithmic density)
+            if (k != P->iss) { std::fprintf(stderr, "pc_oracle: bcz 'cT' only for ss\n"); std::exit(1); }
+            const int il = P->ilnrho;
+            const double tmp = 2 * e.cv * std::log((tb == 0 ? P->cs2bot : P->cs2top) / e.cs20);
+            F(nb, k) = 0.5 * tmp - (e.cp - e.cv) * (F(nb, il) - e.lnrho0);
+            for (int i = 1; i <= NG; ++i)
+              F(nb - dir * i, k) = -F(nb + dir * i, k) + tmp - (e.cp - e.cv) * (F(nb + dir * i, il) + F(nb - dir * i, il) - 2 * e.lnrho0);
+          } break;
+          default: std::fprintf(stderr, "pc_oracle: unknown bcz %d\n", bc); std::exit(1);
+          }
         }
-  }
+    }
 }
 
 void pc_oracle_deriv(const pc_oracle_pars *P, const double *f, int k, int j, int kind, double *out) {
@@ -739,6 +861,7 @@ double pc_oracle_rhs(const pc_oracle_pars *P, const double *f, double *df, int l
             a.dtc = std::max(a.dtc, std::sqrt(p.advec_cs2[i]) / P->cdt);
             if (c.lmagnetic()) a.dtb = std::max(a.dtb, std::sqrt(p.advec_va2[i]) / P->cdt);
             a.dtnu = std::max(a.dtnu, p.diffus_nu[i] / P->cdtv);
+            if (c.lentropy()) a.dtchi = std::max(a.dtchi, p.diffus_chi[i] / P->cdtv);
           }
         }
       }
@@ -753,7 +876,7 @@ double pc_oracle_rhs(const pc_oracle_pars *P, const double *f, double *df, int l
     t.b2m = std::max(t.b2m, a.b2m); t.j2s += a.j2s; t.j2m = std::max(t.j2m, a.j2m);
     t.abs_ += a.abs_; t.jbs += a.jbs; t.ous += a.ous; t.epsKs += a.epsKs; t.sss += a.sss;
     t.dtu = std::max(t.dtu, a.dtu); t.dtc = std::max(t.dtc, a.dtc); t.dtb = std::max(t.dtb, a.dtb);
-    t.dtnu = std::max(t.dtnu, a.dtnu);
+    t.dtnu = std::max(t.dtnu, a.dtnu); t.dtchi = std::max(t.dtchi, a.dtchi);
   }
   if (diag) {
     const double nw = (double)g.nx * g.ny * g.nz; // nwgrid, diagnostics.f90:840-1051
@@ -764,7 +887,7 @@ double pc_oracle_rhs(const pc_oracle_pars *P, const double *f, double *df, int l
     diag->abm = t.abs_ / nw; diag->jbm = t.jbs / nw; diag->oum = t.ous / nw;
     diag->epsK = t.epsKs / nw; diag->ssm = t.sss / nw;
     diag->dtu = t.dtu; diag->dtc = t.dtc; diag->dtb = t.dtb; diag->dtnu = t.dtnu;
-    diag->dt1_max = t.dt1;
+    diag->dt1_max = t.dt1; diag->dtchi = t.dtchi;
   }
   return lcourant ? t.dt1 : 0.0;
 }

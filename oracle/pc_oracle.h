@@ -54,7 +54,21 @@ typedef struct pc_oracle_pars {
   double cdt, cdtv, cdtv2, cdtv3;
   double dtmax; /* equ.f90:270-280: dt1_max initialised to 1/dtmax */
   int nthreads; /* OpenMP threads over (m,n) pencils; <=0 -> default */
+  /* ---- vertically stratified set-ups (samples/conv-slab); all zero = triply periodic box ---- */
+  /* z boundary condition per [bottom/top][variable slot] (boundcond.f90:1421-1787): PC_BC_P 'p', PC_BC_S 's',
+     PC_BC_A 'a', PC_BC_A2 'a2', PC_BC_C1 'c1' (entropy: constant heat flux, entropy_bcs.f90:93-235),
+     PC_BC_CT 'cT' (entropy: constant temperature, eos_idealgas.f90:3112-3260) */
+  int bcz[2][8];
+  double gravz;     /* gravity_simple.f90:521-523 (gravz_profile='const'), addgravity :1083-1162 */
+  double Omega;     /* hydro.f90:6339-6366 coriolis_cartesian, theta=0 */
+  int lheatc_Kprof; /* entropy.f90:1176-1178, calc_heatcond_arrays :5913-6119 */
+  double hcond0, hcond1, hcond2, widthss, z1, z2; /* get_gravz_heatcond entropy.f90:7741-7769 */
+  double cool, wcool, cs2cool, ztop;              /* entropy.f90:1323,1367; get_heat_cool_gravz :6761-6828 */
+  double FbotKbot, FtopKtop;                      /* entropy.f90:854-887 */
+  double cs2bot, cs2top;                          /* density.f90:1605-1610, entropy.f90:818-838 */
 } pc_oracle_pars;
+
+enum { PC_BC_P = 0, PC_BC_S = 1, PC_BC_A = 2, PC_BC_A2 = 3, PC_BC_C1 = 4, PC_BC_CT = 5 };
 
 /* helical forcing coefficients for one step (forcing.f90:1773-2001) */
 typedef struct pc_oracle_forcing {
@@ -68,9 +82,11 @@ typedef struct pc_oracle_diag {
   double urms, umax, rhom, brms, bmax, jrms, jmax, abm, jbm, oum, epsK, ssm;
   double dtu, dtc, dtb, dtnu; /* max(advec_uu)/cdt etc. (not yet multiplied by dt) */
   double dt1_max;
+  double dtchi; /* max(diffus_chi)/cdtv (entropy.f90:4184-4220) */
 } pc_oracle_diag;
 
-/* periodic ghost fill in x, then y, then z (boundcond.f90:2387-2433) */
+/* ghost fill in x, then y (periodic, boundcond.f90:2387-2433), then z (periodic, or bcz bottom then top in
+   variable order, boundcond.f90:1421-1787; 'a' and 'cT' also set the boundary plane itself) */
 void pc_oracle_update_ghosts(const pc_oracle_pars *p, double *f);
 
 /* one derivative of variable k along j (1..3) for the whole interior; out is nx*ny*nz.

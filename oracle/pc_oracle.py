@@ -28,7 +28,18 @@ class Pars(C.Structure):
         ("lupw_uu", C.c_int), ("lupw_lnrho", C.c_int), ("lupw_ss", C.c_int), ("lupw_aa", C.c_int),
         ("cdt", C.c_double), ("cdtv", C.c_double), ("cdtv2", C.c_double), ("cdtv3", C.c_double),
         ("dtmax", C.c_double), ("nthreads", C.c_int),
+        # vertically stratified set-ups (conv-slab): z boundary conditions, gravity, rotation, K-profile, cooling
+        ("bcz", (C.c_int * 8) * 2),
+        ("gravz", C.c_double), ("Omega", C.c_double),
+        ("lheatc_Kprof", C.c_int),
+        ("hcond0", C.c_double), ("hcond1", C.c_double), ("hcond2", C.c_double),
+        ("widthss", C.c_double), ("z1", C.c_double), ("z2", C.c_double),
+        ("cool", C.c_double), ("wcool", C.c_double), ("cs2cool", C.c_double), ("ztop", C.c_double),
+        ("FbotKbot", C.c_double), ("FtopKtop", C.c_double), ("cs2bot", C.c_double), ("cs2top", C.c_double),
     ]
+
+
+BC_CODES = {"p": 0, "s": 1, "a": 2, "a2": 3, "c1": 4, "cT": 5}
 
 
 class Forcing(C.Structure):
@@ -39,7 +50,7 @@ class Forcing(C.Structure):
 class Diag(C.Structure):
     _fields_ = [(n, C.c_double) for n in
                 ("urms", "umax", "rhom", "brms", "bmax", "jrms", "jmax", "abm", "jbm", "oum", "epsK", "ssm",
-                 "dtu", "dtc", "dtb", "dtnu", "dt1_max")]
+                 "dtu", "dtc", "dtb", "dtnu", "dt1_max", "dtchi")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -92,7 +103,12 @@ def _dp(a):
 def pars_from_dict(d, nthreads=0):
     p = Pars()
     for k, v in d.items():
-        if hasattr(p, k):
+        if k == "bcz":  # list of 'bot:top' strings per variable, as in run.in (boundcond.f90:175-260)
+            for j, spec in enumerate(v):
+                bot, _, top = spec.partition(":")
+                p.bcz[0][j] = BC_CODES[bot]
+                p.bcz[1][j] = BC_CODES[top or bot]
+        elif hasattr(p, k):
             setattr(p, k, v)
     p.nthreads = nthreads
     return p
