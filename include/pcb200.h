@@ -58,7 +58,7 @@ typedef struct pcb200_config {
   /* cdata: cdt, cdtv, cdtv2, cdtv3 (global_pushpars.f90:27-32), dtmax */
   double cdt, cdtv, cdtv2, cdtv3;
   double dtmax;
-  /* boundary conditions: only 'p' (periodic) in all directions is supported */
+  /* boundary conditions: x and y must be periodic; z is periodic (lperi[2]=1) or closed (lperi[2]=0, see bcz below) */
   int lperi[3];
   /* device selection: -1 = local rank modulo device count */
   int device;
@@ -67,7 +67,22 @@ typedef struct pcb200_config {
      roles, 4 = 2 with lead/trail z-mixed derivatives, 5 = 4 specialised for dx=dy=dz, 6 / 7 = 5 with
      the z histories of the scalars / of all variables in tensor memory, 8 = 7 with 12 warps on a (32 x 12) tile */
   int kernel_variant;
+  /* ---- vertically stratified set-ups (samples/conv-slab); all zero = triply periodic box --------------------
+     z boundary condition per [bottom/top][variable slot] when lperi[2]=0 (boundcond.f90:1421-1787, bcz12):
+     PCB200_BC_S 's', PCB200_BC_A 'a', PCB200_BC_A2 'a2', PCB200_BC_C1 'c1' (entropy: constant heat flux,
+     entropy_bcs.f90:93-235), PCB200_BC_CT 'cT' (entropy: constant temperature, eos_idealgas.f90:3112-3260).
+     Requires nprocy = nprocz = 1 and selects kernel variant 1. */
+  int bcz[2][8];
+  double gravz;     /* gravity_simple.f90:521-523 gravz_profile='const'; addgravity :1083-1162 */
+  double Omega;     /* hydro.f90:6339-6366 coriolis_cartesian (theta=0) */
+  int lheatc_Kprof; /* iheatcond='K-profile' (entropy.f90:1176-1178, 5913-6151) */
+  double hcond0, hcond1, hcond2, widthss, z1, z2; /* get_gravz_heatcond entropy.f90:7741-7769 */
+  double cool, wcool, cs2cool, ztop;              /* cooling layer, entropy.f90:1323,1367,6761-6828 ('gaussian') */
+  double FbotKbot, FtopKtop;                      /* entropy.f90:854-887 (for 'c1') */
+  double cs2bot, cs2top;                          /* for 'cT' (density.f90:1605-1610, entropy.f90:818-838) */
 } pcb200_config;
+
+enum { PCB200_BC_P = 0, PCB200_BC_S = 1, PCB200_BC_A = 2, PCB200_BC_A2 = 3, PCB200_BC_C1 = 4, PCB200_BC_CT = 5 };
 
 /* must be called before initialize_gpu_c; copies *cfg */
 void pcb200_configure(const pcb200_config *cfg);
@@ -187,7 +202,7 @@ enum {
   PCB200_RED_URMS = 0, PCB200_RED_UMAX, PCB200_RED_RHOM, PCB200_RED_BRMS, PCB200_RED_BMAX,
   PCB200_RED_JRMS, PCB200_RED_JMAX, PCB200_RED_ABM, PCB200_RED_JBM, PCB200_RED_OUM,
   PCB200_RED_EPSK, PCB200_RED_SSM, PCB200_RED_DTU, PCB200_RED_DTC, PCB200_RED_DTB,
-  PCB200_RED_DTNU, PCB200_RED_DT1MAX, PCB200_RED_DT, PCB200_RED_SPARE0, PCB200_RED_SPARE1,
+  PCB200_RED_DTNU, PCB200_RED_DT1MAX, PCB200_RED_DT, PCB200_RED_DTCHI, PCB200_RED_SPARE1,
   PCB200_N_REDUCED = 20
 };
 void get_gpu_reduced_vars_c(double *dst);

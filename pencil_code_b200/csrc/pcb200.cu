@@ -63,7 +63,7 @@ struct UpdateArgs {
   Forcing frc;
 };
 
-template <bool ENT, bool MAG, bool HYP, bool UPW>
+template <bool ENT, bool MAG, bool HYP, bool UPW, bool STRAT = false>
 __global__ void __launch_bounds__(256) rhs_update_v1(const UpdateArgs a) {
   const int ix = blockIdx.x * blockDim.x + threadIdx.x + NG;
   const int iy = blockIdx.y * blockDim.y + threadIdx.y + NG;
@@ -73,7 +73,7 @@ __global__ void __launch_bounds__(256) rhs_update_v1(const UpdateArgs a) {
   GlobalTaps tp{a.fin + o};
   constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
   double rhs[NV];
-  rhs_cell<ENT, MAG, HYP, UPW>(tp, rhs);
+  rhs_cell<ENT, MAG, HYP, UPW, GlobalTaps, STRAT>(tp, rhs, iz - NG);
   const double dtb = (*a.dt_dev) * a.beta;
   double force[3] = {0., 0., 0.};
   if (a.frc.on) { // forcing.f90:2170-2345
@@ -180,6 +180,54 @@ __global__ void ghost_fill_all(double *f, int wy, int wz) {
   b[ix + cP.sy * iy + cP.sz * iz] = b[sx + cP.sy * sy_ + cP.sz * sz_];
 }
 
+// Closed z boundaries (boundconds_z boundcond.f90:1421-1787): one thread per (x,y) column over the whole (mx,my) plane,
+// x and y ghosts included (they have been wrapped before); bottom for all variables in slot order, then top, as the
+// reference does -- the entropy conditions read the density ghost zones of the same side.
+//   's' / 'a' / 'a2'  bc_sym_z boundcond.f90:3842-3900 ('a' also zeroes the boundary plane)
+//   'c1' (ss)         bc_ss_flux entropy_bcs.f90:93-235 (K-profile conduction: tmp_xy = cp*FbotKbot/cs2)
+//   'cT' (ss)         bc_ss_temp_z eos_idealgas.f90:3112-3260 (sets the boundary plane, ln cs2 antisymmetric about it)
+__global__ void bc_z_kernel(double *f) {
+  const Pars &P = cP;
+  const int ix = blockIdx.x * blockDim.x + threadIdx.x, iy = blockIdx.y;
+  if (ix >= P.mx) return;
+  double *c = f + ix + P.sy * iy;
+  const int n1 = NG, n2 = NG + P.nz - 1;
+  const int il = 3, is = 4; // lnrho, ss slots (check_supported)
+  for (int tb = 0; tb < 2; ++tb) {
+    const int nb = tb == 0 ? n1 : n2, dir = tb == 0 ? 1 : -1; // ghost plane nb - dir*i mirrors nb + dir*i
+    for (int k = 0; k < P.nvar; ++k) {
+      double *q = c + k * P.sv;
+      const int bc = P.bcz[tb][k];
+      if (bc == PCB200_BC_S) {
+        for (int i = 1; i <= NG; ++i) q[P.sz * (nb - dir * i)] = q[P.sz * (nb + dir * i)];
+      } else if (bc == PCB200_BC_A) {
+        for (int i = 1; i <= NG; ++i) q[P.sz * (nb - dir * i)] = -q[P.sz * (nb + dir * i)];
+        q[P.sz * nb] = 0.0;
+      } else if (bc == PCB200_BC_A2) {
+        const double b = q[P.sz * nb];
+        for (int i = 1; i <= NG; ++i) q[P.sz * (nb - dir * i)] = 2 * b - q[P.sz * (nb + dir * i)];
+      } else if (bc == PCB200_BC_C1) {
+        const double *l = c + il * P.sv;
+        const double cs2 = P.cs20 * exp(P.gamma_m1 * (l[P.sz * nb] - P.lnrho0) + P.cv1 * q[P.sz * nb]);
+        const double tmp = (tb == 0 ? P.cpFbotKbot : P.cpFtopKtop) / cs2;
+        for (int i = 1; i <= NG; ++i) {
+          const double dlnrho = l[P.sz * (nb + i)] - l[P.sz * (nb - i)]; // getdlnrho_z density_methods.f90:409-426
+          const double dz2 = 2. * (i * P.dz);                             // dz2_bound grid.f90:3149-3151
+          if (tb == 0) q[P.sz * (nb - i)] = q[P.sz * (nb + i)] + P.cp_cv * (dlnrho + dz2 * tmp);
+          else q[P.sz * (nb + i)] = q[P.sz * (nb - i)] + P.cp_cv * (-dlnrho - dz2 * tmp);
+        }
+      } else if (bc == PCB200_BC_CT) {
+        const double *l = c + il * P.sv;
+        const double tmp = P.cT_tmp[tb];
+        q[P.sz * nb] = 0.5 * tmp - P.cp_cv * (l[P.sz * nb] - P.lnrho0);
+        for (int i = 1; i <= NG; ++i)
+          q[P.sz * (nb - dir * i)] = -q[P.sz * (nb + dir * i)] + tmp - P.cp_cv * (l[P.sz * (nb + dir * i)] + l[P.sz * (nb - dir * i)] - 2 * P.lnrho0);
+      }
+    }
+  }
+  (void)is;
+}
+
 // y-face pack/unpack for yz-pencil decompositions (mpicomm.f90:1604-1731: y-slabs f(:,m1:m1i,n1:n2,:)
 // are mx wide, i.e. carry the x ghosts).  buf[k][izl][r][ix], rows row0..row0+2, interior z only.
 __global__ void pack_y(const double *__restrict__ f, double *__restrict__ buf, int row0, int nvar) {
@@ -218,7 +266,7 @@ template <bool ENT, bool MAG> __global__ void __launch_bounds__(RED_THREADS) cfl
     const long long r = c / cP.nx;
     const int iy = (int)(r % cP.ny) + NG, iz = (int)(r / cP.ny) + NG;
     GlobalTaps tp{f + ix + cP.sy * iy + cP.sz * iz};
-    m = fmax(m, cfl_cell<ENT, MAG>(tp).dt1);
+    m = fmax(m, cfl_cell<ENT, MAG>(tp, iz - NG).dt1);
   }
   m = warp_max(m);
   if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
@@ -263,7 +311,7 @@ __global__ void __launch_bounds__(RED_THREADS) diag_kernel(const double *f, doub
     const int iy = (int)(r % cP.ny) + NG, iz = (int)(r / cP.ny) + NG;
     GlobalTaps tp{f + ix + cP.sy * iy + cP.sz * iz};
     double cs[DS_NSUM], cm[DM_NMAX];
-    diag_cell<ENT, MAG>(tp, cs, cm);
+    diag_cell<ENT, MAG>(tp, cs, cm, iz - NG);
 #pragma unroll
     for (int i = 0; i < DS_NSUM; ++i) s[i] += cs[i];
 #pragma unroll
@@ -438,6 +486,7 @@ struct State {
   int ldt = 0;
   double *dt_dev = nullptr, *dt1_dev = nullptr;
   double *pinned = nullptr; // small pinned scratch (32 doubles)
+  double *zprof_dev = nullptr; // [3][nz]: hcond, dlnhcond/dz, profz_cool of the interior planes (stratified runs)
   // reductions
   double *partial = nullptr;
   int red_blocks = 0;
@@ -516,6 +565,48 @@ static void derive_pars() {
   P.lupw_uu = c.lupw_uu; P.lupw_lnrho = c.lupw_lnrho; P.lupw_ss = c.lupw_ss; P.lupw_aa = c.lupw_aa;
   P.mcs20g1 = -(P.cs20 * P.gamma1); P.chicp = P.chi * P.cp; P.nu2 = 2 * P.nu; P.etamu0 = P.eta * P.mu0; P.nu13 = P.nu * (1. / 3.);
   for (int i = 0; i < 3; ++i) P.dmcu[i] = c.lvisc_nu_const ? (c.nu * (1. / 3.)) * P.dmc[0][i] : 0.0;
+  // vertically stratified set-ups
+  P.lheatc_Kprof = c.lheatc_Kprof; P.lcool = c.cool != 0.0;
+  P.lstrat = (c.gravz != 0.0 || c.Omega != 0.0 || c.lheatc_Kprof || c.cool != 0.0) ? 1 : 0;
+  for (int tb = 0; tb < 2; ++tb)
+    for (int k = 0; k < MAXVAR; ++k) P.bcz[tb][k] = c.lperi[2] ? PCB200_BC_P : c.bcz[tb][k];
+  P.gravz = c.gravz; P.c2omega = 2 * c.Omega;
+  P.cs2cool_ = c.cs2cool; P.cs2cool1 = c.cs2cool != 0.0 ? 1.0 / c.cs2cool : 0.0;
+  const double cv = P.gamma1 * P.cp; // eos_idealgas.f90:154-270
+  P.cp_cv = P.cp - cv;
+  P.cpFbotKbot = P.cp * c.FbotKbot; P.cpFtopKtop = P.cp * c.FtopKtop;
+  P.cT_tmp[0] = c.cs2bot > 0 ? 2 * cv * std::log(c.cs2bot / c.cs20) : 0.0;
+  P.cT_tmp[1] = c.cs2top > 0 ? 2 * cv * std::log(c.cs2top / c.cs20) : 0.0;
+  P.dz = c.dz;
+  P.zprof = S.zprof_dev;
+}
+
+// z profiles of the stratified terms on the interior planes of this rank: get_gravz_heatcond entropy.f90:7741-7769
+// (step, der_step sub.f90:4957-5015) and the cooling profile 'gaussian' entropy.f90:1323,1367
+static void upload_zprof(cudaStream_t st) {
+  const pcb200_config &c = S.cfg;
+  if (!S.zprof_dev) return;
+  static std::vector<double> h; // must outlive the asynchronous copy
+  h.assign((size_t)3 * c.nz, 0.0);
+  auto step = [](double x, double x0, double w) { return 0.5 * (1 + std::tanh((x - x0) / w)); };
+  auto der_step = [](double x, double x0, double w) {
+    const double arg = std::fabs((x - x0) / w);
+    return arg >= 8. ? 2. / w * std::exp(-2. * arg) : 0.5 / (w * std::cosh(arg) * std::cosh(arg));
+  };
+  for (int n = 0; n < c.nz; ++n) {
+    const double z = c.z0 + n * c.dz;
+    if (c.lheatc_Kprof) {
+      const double p = 1. + (c.hcond1 - 1.) * step(z, c.z1, -c.widthss) + (c.hcond2 - 1.) * step(z, c.z2, c.widthss);
+      h[c.nz + n] = ((c.hcond1 - 1.) * der_step(z, c.z1, -c.widthss) + (c.hcond2 - 1.) * der_step(z, c.z2, c.widthss)) / p;
+      h[n] = c.hcond0 * p;
+    }
+    if (c.cool != 0.0) {
+      const double q = (c.ztop - z) / c.wcool;
+      h[2 * c.nz + n] = c.cool * std::exp(-0.5 * (q * q));
+    }
+  }
+  CK(cudaMemcpyAsync(S.zprof_dev, h.data(), h.size() * sizeof(double), cudaMemcpyHostToDevice, st));
+  SYNC_STREAM((st));
 }
 
 static void check_supported() {
@@ -526,7 +617,27 @@ static void check_supported() {
   if (c.nprocx != 1) die("nprocx must be 1 (z-slab / yz-pencil decomposition only)");
   if (c.nprocy < 1 || c.nprocz < 1) die("bad decomposition %d x %d", c.nprocy, c.nprocz);
   if (c.ipy < 0 || c.ipy >= c.nprocy || c.ipz < 0 || c.ipz >= c.nprocz) die("rank position (%d,%d) outside %d x %d", c.ipy, c.ipz, c.nprocy, c.nprocz);
-  if (!(c.lperi[0] && c.lperi[1] && c.lperi[2])) die("only periodic boundary conditions ('p') are supported");
+  if (!(c.lperi[0] && c.lperi[1])) die("x and y must be periodic ('p')");
+  const bool strat = c.gravz != 0.0 || c.Omega != 0.0 || c.lheatc_Kprof || c.cool != 0.0;
+  if (!c.lperi[2] || strat) {
+    if (c.nprocy != 1 || c.nprocz != 1) die("closed z boundaries / stratified terms need nprocy = nprocz = 1");
+    if (c.kernel_variant > 1) die("closed z boundaries / stratified terms are implemented by kernel variant 1 only");
+  }
+  if (!c.lperi[2]) {
+    for (int tb = 0; tb < 2; ++tb)
+      for (int k = 0; k < c.nvar; ++k) {
+        const int bc = c.bcz[tb][k];
+        if (bc != PCB200_BC_S && bc != PCB200_BC_A && bc != PCB200_BC_A2 && bc != PCB200_BC_C1 && bc != PCB200_BC_CT)
+          die("bcz(%d,%s)=%d is not supported (s, a, a2, c1, cT)", k + 1, tb ? "top" : "bot", bc);
+        if ((bc == PCB200_BC_C1 || bc == PCB200_BC_CT) && k != c.iss) die("bcz 'c1' / 'cT' are implemented for the entropy only");
+        if (bc == PCB200_BC_C1 && c.lheatc_chiconst) die("bcz 'c1' with chi-const conduction is not supported");
+        if (bc == PCB200_BC_CT && (tb ? c.cs2top : c.cs2bot) <= 0.0) die("bcz 'cT' needs cs2%s > 0", tb ? "top" : "bot");
+      }
+    if (c.nz < 2 * NG + 1) die("closed z boundaries need nz >= 7");
+  }
+  if ((c.lheatc_Kprof || c.cool != 0.0) && c.iss < 0) die("K-profile conduction / cooling need the entropy module");
+  if (c.lheatc_Kprof && c.widthss == 0.0) die("K-profile conduction needs widthss /= 0");
+  if (c.cool != 0.0 && (c.wcool == 0.0 || c.cs2cool == 0.0)) die("cooling needs wcool, cs2cool /= 0");
   if (c.iux != 0 || c.ilnrho != 3) die("hydro (slots 1-3) and density (slot 4) are required in registration order");
   const bool ent = c.iss >= 0, mag = c.iax >= 0;
   if (ent && c.iss != 4) die("iss must be slot 5");
@@ -564,7 +675,8 @@ static void make_tensor_map(CUtensorMap *tm, double *base, int box_x = V2_HX, in
 template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v1(const UpdateArgs &a, cudaStream_t st) {
   dim3 b(64, 4, 1);
   dim3 g((S.P.nx + b.x - 1) / b.x, (S.P.ny + b.y - 1) / b.y, (a.z_hi - a.z_lo + b.z - 1) / b.z);
-  rhs_update_v1<ENT, MAG, HYP, UPW><<<g, b, 0, st>>>(a);
+  if (S.P.lstrat) rhs_update_v1<ENT, MAG, HYP, UPW, true><<<g, b, 0, st>>>(a);
+  else rhs_update_v1<ENT, MAG, HYP, UPW><<<g, b, 0, st>>>(a);
 }
 
 template <bool ENT, bool MAG, bool HYP, bool UPW, bool TRAIL = false> static void launch_update_v2(const UpdateArgs &a, cudaStream_t st) {
@@ -891,6 +1003,14 @@ static void wait_halo(cudaStream_t st) {
 }
 // make all ghost zones of buffer f valid (x wrap locally; y and z wrap or exchange), in stream order
 static void update_ghosts(double *f, cudaStream_t st) {
+  if (!S.cfg.lperi[2]) { // closed in z: wrap x and y, then the z conditions on whole planes
+    if (P_ghost_ok()) launch_ghost_all(f, true, false, st);
+    else { launch_ghost(f, 0, st); launch_ghost(f, 1, st); }
+    bc_z_kernel<<<dim3((S.P.mx + 63) / 64, S.P.my), 64, 0, st>>>(f);
+    CK(cudaGetLastError());
+    S.launches++;
+    return;
+  }
   if (S.cfg.nprocy == 1 && S.cfg.nprocz == 1 && !S.loopback && P_ghost_ok()) { launch_ghost_all(f, true, true, st); return; }
   update_ghosts_xy(f, st);
   if (S.cfg.nprocz == 1 && !S.loopback) launch_ghost(f, 2, st);
@@ -962,6 +1082,7 @@ static void compute_diagnostics(cudaStream_t st) {
   r[PCB200_RED_DTC] = m[DM_DTC];
   r[PCB200_RED_DTB] = m[DM_DTB];
   r[PCB200_RED_DTNU] = m[DM_DTNU];
+  r[PCB200_RED_DTCHI] = m[DM_DTCHI];
   S.diag_valid = true;
 }
 
@@ -1233,10 +1354,12 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
     if (kv != 0 && kv != 1 && kv != 4 && kv != 5 && kv != 9 && kv != 10) die("kernel_variant=%d unknown (0 = auto, 1, 4, 5, 9, 10)", kv);
     if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
     const bool iso = S.cfg.dx == S.cfg.dy && S.cfg.dy == S.cfg.dz; // variants >= 5 share one set of stencil weights
-    S.variant = kv ? kv : (tma_ok ? (iso ? 10 : 4) : 1);
+    const bool strat = !S.cfg.lperi[2] || S.cfg.gravz != 0.0 || S.cfg.Omega != 0.0 || S.cfg.lheatc_Kprof || S.cfg.cool != 0.0;
+    S.variant = kv ? kv : (tma_ok && !strat ? (iso ? 10 : 4) : 1);
     if (S.variant >= 5 && !iso) S.variant = 4; // anisotropic spacing: same kernel structure with per-direction weights
     S.xpad = S.variant == 10 ? 1 : 0;
   }
+  CK(cudaMalloc(&S.zprof_dev, sizeof(double) * 3 * S.cfg.nz));
   derive_pars();
   const Pars &P = S.P;
   S.host_f = f;
@@ -1322,6 +1445,7 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   S.fz_dev = S.fy_dev + P.my;
   CK(cudaMalloc(&S.fpq_dev, sizeof(double) * 6 * P.mz));
   CK(cudaMemcpyToSymbolAsync(cP, &S.P, sizeof(Pars), 0, cudaMemcpyHostToDevice, S.stream));
+  upload_zprof(S.stream);
   S.pinned[0] = S.dt_host;
   CK(cudaMemcpyAsync(S.dt_dev, S.pinned, sizeof(double), cudaMemcpyHostToDevice, S.stream));
   SYNC_STREAM((S.stream));
@@ -1347,7 +1471,7 @@ extern "C" void finalize_gpu_c(void) {
   if (S.flags) { cudaFree(S.flags); cudaFree(S.seq_slots); }
   cudaFree(S.f_alloc[0]); cudaFree(S.f_alloc[1]); cudaFree(S.df_alloc);
   if (S.ybuf) cudaFree(S.ybuf);
-  cudaFree(S.dt_dev); cudaFree(S.dt1_dev); cudaFree(S.partial); cudaFree(S.diag_dev); cudaFree(S.fx_dev); cudaFree(S.fpq_dev);
+  cudaFree(S.dt_dev); cudaFree(S.dt1_dev); cudaFree(S.zprof_dev); S.zprof_dev = nullptr; cudaFree(S.partial); cudaFree(S.diag_dev); cudaFree(S.fx_dev); cudaFree(S.fpq_dev);
   cudaFreeHost(S.pinned);
   cudaEventDestroy(S.ev_ready); cudaEventDestroy(S.ev_halo);
   cudaStreamDestroy(S.comm_stream);
@@ -1447,6 +1571,7 @@ extern "C" void reload_gpu_config_c(void) {
   derive_pars();
   SYNC_STREAM((S.stream));
   CK(cudaMemcpyToSymbol(cP, &S.P, sizeof(Pars)));
+  upload_zprof(S.stream);
 }
 FTN_ALIAS(reload_gpu_config_c)
 

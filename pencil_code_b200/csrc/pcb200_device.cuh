@@ -50,6 +50,16 @@ struct Pars {
   int lvisc_nu_const, lvisc_hyper3_simplified, lvisc_hyper3_nu_const, ldiff_hyper3lnrho;
   int lheatc_chiconst, lviscosity_heat, lresi_eta_const, lohmic_heat, llorentzforce;
   int lupw_uu, lupw_lnrho, lupw_ss, lupw_aa;
+  // vertically stratified set-ups (template flag STRAT of variant 1): constant gravity, Coriolis force (theta=0),
+  // K-profile conduction, cooling layer; closed z boundaries
+  int lstrat, lheatc_Kprof, lcool;
+  int bcz[2][MAXVAR];
+  double gravz, c2omega, cs2cool1;      // 2*Omega, 1/cs2cool (cs2cool itself is cs2cool_)
+  double cs2cool_;
+  const double *zprof;                   // device: hcond(n), dlnhcond/dz(n), profz_cool(n), n = 0..nz-1 (interior planes)
+  double cp_cv, cpFbotKbot, cpFtopKtop;  // cp-cv ; cp*Fbot/Kbot, cp*Ftop/Ktop ('c1')
+  double cT_tmp[2];                      // 2*cv*log(cs2bot/cs20), 2*cv*log(cs2top/cs20) ('cT')
+  double dz;
 };
 
 __constant__ Pars cP; // single translation unit
@@ -138,8 +148,9 @@ template <class T> __device__ __forceinline__ double upwind_sum(const T &tp, int
 // ---------------------------------------------------------------------------
 // Full right-hand side of all variables at one cell.
 // ---------------------------------------------------------------------------
-template <bool ENT, bool MAG, bool HYP, bool UPW, class T>
-__device__ __forceinline__ void rhs_cell(const T &tp, double *__restrict__ rhs) {
+// STRAT (with n = interior z index of the cell): gravity, Coriolis force, K-profile conduction, cooling layer
+template <bool ENT, bool MAG, bool HYP, bool UPW, class T, bool STRAT = false>
+__device__ __forceinline__ void rhs_cell(const T &tp, double *__restrict__ rhs, int n = 0) {
   typedef Slots<ENT> S;
   const Pars &P = cP;
 
@@ -249,7 +260,13 @@ __device__ __forceinline__ void rhs_cell(const T &tp, double *__restrict__ rhs) 
   // ---- momentum: df_u = -ugu + fvisc + fpres (+ jxbr)
   double ru[3];
 #pragma unroll
-  for (int i = 0; i < 3; ++i) ru[i] = ((-ugu[i]) + fvisc[i]) + fpres[i];
+  for (int i = 0; i < 3; ++i) ru[i] = -ugu[i];
+  if (STRAT) { // coriolis_cartesian hydro.f90:6339-6366 (theta=0)
+    ru[0] += P.c2omega * u[1];
+    ru[1] -= P.c2omega * u[0];
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) ru[i] = (ru[i] + fvisc[i]) + fpres[i];
 
   // ---- continuity (density.f90:2887-3060, 3197-3288)
   double rl = (-divu) - uglnrho;
@@ -263,12 +280,25 @@ __device__ __forceinline__ void rhs_cell(const T &tp, double *__restrict__ rhs) 
     if (UPW && P.lupw_ss) ugss -= upwind_sum(tp, S::ISS, u, -1);
     rs = -ugss;
     if (P.lviscosity_heat) rs += TT1 * (2 * P.nu * sij2); // viscosity.f90:2743-2789
-    if (P.lheatc_chiconst) {                             // entropy.f90:4852-4947
+    const bool kprof = STRAT && P.lheatc_Kprof;
+    double del2lnTT = 0.0;
+    if (P.lheatc_chiconst || kprof) {
       const double del2lnrho = tp.d2(S::ILN, 0) + tp.d2(S::ILN, 1) + tp.d2(S::ILN, 2);
       const double del2ss = tp.d2(S::ISS, 0) + tp.d2(S::ISS, 1) + tp.d2(S::ISS, 2);
-      const double del2lnTT = P.gamma_m1 * del2lnrho + P.cv1 * del2ss;
+      del2lnTT = P.gamma_m1 * del2lnrho + P.cv1 * del2ss;
+    }
+    if (kprof) { // calc_heatcond_arrays entropy.f90:5913-6119: rho1*hcond*(del2lnTT + glnTT.(glnTT+glhc))
+      const double hcond = __ldg(P.zprof + n), glhc = __ldg(P.zprof + P.nz + n);
+      const double g2 = glnTT[0] * glnTT[0] + glnTT[1] * glnTT[1] + glnTT[2] * (glnTT[2] + glhc);
+      rs += exp(-lnrho) * hcond * (del2lnTT + g2);
+    }
+    if (P.lheatc_chiconst) {                             // entropy.f90:4852-4947
       const double g2 = (gl[0] + glnTT[0]) * glnTT[0] + (gl[1] + glnTT[1]) * glnTT[1] + (gl[2] + glnTT[2]) * glnTT[2];
       rs += P.chi * P.cp * (del2lnTT + g2);
+    }
+    if (STRAT && P.lcool) { // get_heat_cool_gravz entropy.f90:6761-6828 + calc_heat_cool :6553
+      const double heat = -__ldg(P.zprof + 2 * P.nz + n) * (cs2 - P.cs2cool_) * P.cs2cool1;
+      rs += TT1 * exp(-lnrho) * heat;
     }
   }
 
@@ -338,6 +368,7 @@ __device__ __forceinline__ void rhs_cell(const T &tp, double *__restrict__ rhs) 
     }
   }
   if (ENT) rhs[S::ISS] = rs;
+  if (STRAT) ru[2] += P.gravz; // addgravity gravity_simple.f90:1083-1162
 #pragma unroll
   for (int i = 0; i < 3; ++i) rhs[S::IUX + i] = ru[i];
 }
@@ -347,9 +378,10 @@ __device__ __forceinline__ void rhs_cell(const T &tp, double *__restrict__ rhs) 
 // magnetic.f90:5160-5217, viscosity.f90:2433-2459, entropy.f90:4852-4947)
 // ---------------------------------------------------------------------------
 struct CflParts {
-  double dt1, advec_uu, advec_cs2, advec_va2;
+  double dt1, advec_uu, advec_cs2, advec_va2, diffus_chi;
 };
-template <bool ENT, bool MAG, class T> __device__ __forceinline__ CflParts cfl_cell(const T &tp) {
+// n: interior z index of the cell (K-profile conduction only)
+template <bool ENT, bool MAG, class T> __device__ __forceinline__ CflParts cfl_cell(const T &tp, int n) {
   typedef Slots<ENT> S;
   const Pars &P = cP;
   CflParts r;
@@ -377,7 +409,10 @@ template <bool ENT, bool MAG, class T> __device__ __forceinline__ CflParts cfl_c
     maxdiffus3 = fmax(maxdiffus3, d3 * P.dxyz_6);
   }
   if (P.ldiff_hyper3lnrho) maxdiffus3 = fmax(maxdiffus3, P.diffrho_hyper3 * P.dxyz_6);
-  if (ENT && P.lheatc_chiconst) maxdiffus = fmax(maxdiffus, (P.gamma * P.chi) * P.dxyz_2);
+  r.diffus_chi = 0.0; // entropy.f90:3789,3826-3829: the conduction terms add up before the max
+  if (ENT && P.lstrat && P.lheatc_Kprof) r.diffus_chi += (exp(-lnrho) * __ldg(P.zprof + n) * P.cv1) * P.dxyz_2;
+  if (ENT && P.lheatc_chiconst) r.diffus_chi += (P.gamma * P.chi) * P.dxyz_2;
+  maxdiffus = fmax(maxdiffus, r.diffus_chi);
   if (MAG) maxdiffus = fmax(maxdiffus, P.eta * P.dxyz_2);
   const double a = maxadvec / P.cdt;
   const double d = maxdiffus / P.cdtv + maxdiffus3 / P.cdtv3;
@@ -389,10 +424,10 @@ template <bool ENT, bool MAG, class T> __device__ __forceinline__ CflParts cfl_c
 // time-series diagnostics per cell
 // ---------------------------------------------------------------------------
 enum { DS_U2 = 0, DS_RHO, DS_OU, DS_EPSK, DS_SS, DS_B2, DS_J2, DS_AB, DS_JB, DS_NSUM };
-enum { DM_U2 = 0, DM_B2, DM_J2, DM_DTU, DM_DTC, DM_DTB, DM_DTNU, DM_NMAX };
+enum { DM_U2 = 0, DM_B2, DM_J2, DM_DTU, DM_DTC, DM_DTB, DM_DTNU, DM_DTCHI, DM_NMAX };
 
 template <bool ENT, bool MAG, class T>
-__device__ __forceinline__ void diag_cell(const T &tp, double *__restrict__ sums, double *__restrict__ maxs) {
+__device__ __forceinline__ void diag_cell(const T &tp, double *__restrict__ sums, double *__restrict__ maxs, int n) {
   typedef Slots<ENT> S;
   const Pars &P = cP;
   double u[3], uij[3][3];
@@ -448,7 +483,8 @@ __device__ __forceinline__ void diag_cell(const T &tp, double *__restrict__ sums
     maxs[DM_B2] = b2;
     maxs[DM_J2] = jsq;
   }
-  const CflParts c = cfl_cell<ENT, MAG>(tp);
+  const CflParts c = cfl_cell<ENT, MAG>(tp, n);
+  maxs[DM_DTCHI] = c.diffus_chi / P.cdtv;
   maxs[DM_DTU] = c.advec_uu / P.cdt;
   maxs[DM_DTC] = sqrt(c.advec_cs2) / P.cdt;
   maxs[DM_DTB] = sqrt(c.advec_va2) / P.cdt;

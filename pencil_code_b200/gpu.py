@@ -19,7 +19,8 @@ LIB_PATH = os.path.join(_PKG, "libpcb200.so")
 
 N_GPU_REDUCED_VARS = 20  # gpu.h:12
 REDUCED_NAMES = ("urms", "umax", "rhom", "brms", "bmax", "jrms", "jmax", "abm", "jbm", "oum", "epsK", "ssm",
-                 "dtu", "dtc", "dtb", "dtnu", "dt1_max", "dt", "spare0", "spare1")
+                 "dtu", "dtc", "dtb", "dtnu", "dt1_max", "dt", "dtchi", "spare1")
+BC_CODES = {"p": 0, "s": 1, "a": 2, "a2": 3, "c1": 4, "cT": 5}  # include/pcb200.h PCB200_BC_*
 
 
 class Config(C.Structure):
@@ -44,6 +45,13 @@ class Config(C.Structure):
         ("dtmax", C.c_double),
         ("lperi", C.c_int * 3),
         ("device", C.c_int), ("kernel_variant", C.c_int),
+        ("bcz", (C.c_int * 8) * 2),
+        ("gravz", C.c_double), ("Omega", C.c_double),
+        ("lheatc_Kprof", C.c_int),
+        ("hcond0", C.c_double), ("hcond1", C.c_double), ("hcond2", C.c_double),
+        ("widthss", C.c_double), ("z1", C.c_double), ("z2", C.c_double),
+        ("cool", C.c_double), ("wcool", C.c_double), ("cs2cool", C.c_double), ("ztop", C.c_double),
+        ("FbotKbot", C.c_double), ("FtopKtop", C.c_double), ("cs2bot", C.c_double), ("cs2top", C.c_double),
     ]
 
 
@@ -142,11 +150,17 @@ def _dp(a):
 def make_struct(cfg):
     c = Config()
     for name, _ in Config._fields_:
-        if name == "lperi":
+        if name in ("lperi", "bcz"):
             continue
         if name in cfg:
             setattr(c, name, cfg[name])
-    lp = cfg.get("lperi", (1, 1, 1))
+    closed_z = False
+    for j, spec in enumerate(cfg.get("bcz", ())):  # 'bot:top' per variable as in run.in (boundcond.f90:175-260)
+        bot, _, top = spec.partition(":")
+        c.bcz[0][j] = BC_CODES[bot]
+        c.bcz[1][j] = BC_CODES[top or bot]
+        closed_z = closed_z or c.bcz[0][j] != 0 or c.bcz[1][j] != 0
+    lp = cfg.get("lperi", (1, 1, 0 if closed_z else 1))
     c.lperi[0], c.lperi[1], c.lperi[2] = [int(v) for v in lp]
     return c
 
