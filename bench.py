@@ -186,6 +186,7 @@ def main():
     ap.add_argument("--size", "--n", dest="n", type=int, default=512, help="global grid n^3 (use --size under torchrun: --n is ambiguous there)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--e2e-it1", type=int, default=10, help="steps per asynchronous snapshot copy of the second e2e figure (0 = skip)")
     ap.add_argument("--kernel-variant", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="mhd_entropy", choices=["mhd_entropy", "iso_mhd", "hydro_hyper3"],
@@ -323,6 +324,29 @@ def main():
     e2e_value = cells_global * 3 * args.e2e_steps / (ms_e2e * 1e-3)
     finite = bool(np.isfinite(fh[:, 3:-3, 3:-3, 3:-3]).all())
 
+    # ---- the same at the reference's real cadence: the f-array stays on the device and comes back every it1-th step
+    # only (run.f90: lout steps; samples/*/run.in it1=10), as an asynchronous snapshot copy that overlaps the next steps
+    # (pcb200_copy_farray_async: device snapshot + D2H on a copy stream, gpu_astaroth.f90:390-412 nowait_ protocol)
+    it1 = args.e2e_it1
+    e2e_cadence = None
+    if it1 > 0:
+        g.synchronize()
+        barrier()
+        t_c0 = time.perf_counter()
+        g.copy_farray_from_GPU_async(fh)
+        for _ in range(it1):
+            _, t = step(t)
+        g.copy_farray_wait()
+        g.synchronize()
+        ms_c = (time.perf_counter() - t_c0) * 1e3
+        tm3 = torch.tensor([ms_c], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tm3, op=dist.ReduceOp.MAX)
+        ms_c = float(tm3.item())
+        e2e_cadence = {"value": cells_global * 3 * it1 / (ms_c * 1e-3), "unit": UNIT, "it1": it1, "ms_per_step": ms_c / it1,
+                       "h2d_bytes_per_step": 0, "d2h_bytes_per_step": nbytes_f * world / it1,
+                       "path": "f resident on the device; copy_farray_from_GPU(nowait) once per it1 steps, overlapped with the steps"}
+
     # ---- roofline of the dominant kernel (fused rhs+rk), measured live with CUDA events
     peak, peak_src = hbm_peak()
     cells_local = cfg["nx"] * cfg["ny"] * cfg["nz"]
@@ -350,7 +374,7 @@ def main():
     g.time_step(fh, dt, False, t, forcing=forcing.draw(dt), diagnostics=True)
     red = g.get_gpu_reduced_vars()
     checksum = {k: red[k] for k in ("urms", "umax", "rhom", "brms", "jrms", "abm", "ssm") if k in red}
-    checksum["after_steps"] = args.warmup + args.steps + args.e2e_steps
+    checksum["after_steps"] = args.warmup + args.steps + args.e2e_steps + max(args.e2e_it1, 0) + 1
 
     if world > 1:
         barrier()  # nobody frees ghost planes a neighbour may still be writing to
@@ -372,6 +396,7 @@ def main():
                     "d2h_bytes_per_step": nbytes_f * world, "steps": args.e2e_steps,
                     "ms_per_step": ms_e2e / args.e2e_steps,
                     "path": "load_farray_to_GPU + 3 x rhs_GPU + copy_farray_from_GPU per step, pinned host f-array"},
+            "e2e_at_output_cadence": e2e_cadence,
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": roofline,

@@ -48,7 +48,17 @@ module GPU
     real(c_double) :: dtmax
     integer(c_int) :: lperi(3)
     integer(c_int) :: device, kernel_variant
+    integer(c_int) :: bcz(8,2)          ! C: bcz[2][8] (bottom/top, variable slot)
+    real(c_double) :: gravz, Omega
+    integer(c_int) :: lheatc_Kprof
+    real(c_double) :: hcond0, hcond1, hcond2, widthss, z1, z2
+    real(c_double) :: cool, wcool, cs2cool, ztop
+    real(c_double) :: FbotKbot, FtopKtop
+    real(c_double) :: cs2bot, cs2top
   endtype pcb200_config
+
+  ! PCB200_BC_* of include/pcb200.h
+  integer, parameter :: PCB200_BC_P=0, PCB200_BC_S=1, PCB200_BC_A=2, PCB200_BC_A2=3, PCB200_BC_C1=4, PCB200_BC_CT=5
 
   interface
     subroutine pcb200_configure(cfg) bind(C,name="pcb200_configure")
@@ -59,6 +69,11 @@ module GPU
       import :: pcb200_config
       type(pcb200_config), intent(inout) :: cfg
     endsubroutine
+    function pcb200_fill_strat_pars_c(cfg) bind(C,name="pcb200_fill_strat_pars_c") result(ok)
+      import :: pcb200_config, c_int
+      type(pcb200_config), intent(inout) :: cfg
+      integer(c_int) :: ok
+    endfunction
     subroutine pcb200_set_dt(dt,ldt) bind(C,name="pcb200_set_dt")
       import :: c_double, c_int
       real(c_double), intent(in) :: dt
@@ -206,7 +221,7 @@ contains
       character(LEN=512) :: str
       character(kind=c_char), dimension(128) :: nccl_id
       character(LEN=128) :: idbuf
-      integer :: i, zero
+      integer :: i, j, zero
       integer(c_int) :: rank, nranks
 
       str=''
@@ -217,7 +232,6 @@ contains
       if (lanelastic)    str=trim(str)//', '//'anelastic'
       if (lboussinesq)   str=trim(str)//', '//'boussinesq'
       if (lshear)        str=trim(str)//', '//'shear'
-      if (lgrav)         str=trim(str)//', '//'gravity'
       if (lshock)        str=trim(str)//', '//'shock'
       if (lradiation)    str=trim(str)//', '//'radiation'
       if (lchemistry)    str=trim(str)//', '//'chemistry'
@@ -235,7 +249,10 @@ contains
                                     trim(str(3:))//'"')
       if (.not.lcartesian_coords) call fatal_error('initialize_GPU','gpu_b200: Cartesian coordinates only')
       if (.not.all(lequidist))    call fatal_error('initialize_GPU','gpu_b200: equidistant grids only')
-      if (.not.all(lperi))        call fatal_error('initialize_GPU','gpu_b200: periodic boundaries only')
+      if (.not.all(lperi(1:2)))   call fatal_error('initialize_GPU','gpu_b200: x and y must be periodic')
+      if (.not.lperi(3).and.(nprocy/=1.or.nprocz/=1)) &
+                                  call fatal_error('initialize_GPU','gpu_b200: closed z boundaries need nprocy=nprocz=1')
+      if (Omega/=0..and.theta/=0.) call fatal_error('initialize_GPU','gpu_b200: Coriolis force for theta=0 only')
       if (nprocx/=1)              call fatal_error('initialize_GPU','gpu_b200: nprocx must be 1')
       if (itorder/=3)             call fatal_error('initialize_GPU','gpu_b200: itorder=3 only')
       if (ddt>0.)                 call fatal_error('initialize_GPU','gpu_b200: time-step growth limiter (ddt>0) not supported')
@@ -267,9 +284,34 @@ contains
       cfg%device=gpu_device
       cfg%kernel_variant=kernel_variant
 !
-!  nu, eta, chi, eos constants, upwinding and heating switches: via pushpars2c tables (C shim).
+!  z boundary conditions (bcz12 of Cdata, boundcond.f90:1421-1787) and rotation (Omega, theta of Cdata).
+!
+      cfg%bcz=PCB200_BC_P
+      if (.not.lperi(3)) then
+        do j=1,2; do i=1,mvar
+          select case (bcz12(i,j))
+          case ('s');  cfg%bcz(i,j)=PCB200_BC_S
+          case ('a');  cfg%bcz(i,j)=PCB200_BC_A
+          case ('a2'); cfg%bcz(i,j)=PCB200_BC_A2
+          case ('c1'); cfg%bcz(i,j)=PCB200_BC_C1
+          case ('cT'); cfg%bcz(i,j)=PCB200_BC_CT
+          case default
+            call fatal_error('initialize_GPU','gpu_b200: bcz="'//trim(bcz12(i,j))//'" not supported (s, a, a2, c1, cT)')
+          endselect
+        enddo; enddo
+      endif
+      cfg%Omega=Omega
+      cfg%ztop=xyz1(3)
+!
+!  nu, eta, chi, eos constants, upwinding and heating switches, gravity, K-profile conduction and the cooling layer:
+!  via pushpars2c tables (C shim; it refuses gravity / heating set-ups other than the ones implemented).
 !
       call pcb200_fill_physics_pars_c(cfg)
+      if (lgrav) then
+        if (pcb200_fill_strat_pars_c(cfg)==0) call fatal_error('initialize_GPU', &
+            "gpu_b200: gravity only as gravz_profile='const' (no x, y gravity); heating/cooling only as the 'gaussian' "// &
+            "cooling layer (luminosity=0, lcooling_general=F); conduction only 'chi-const' or 'K-profile' (lmultilayer=T)")
+      endif
       call pcb200_configure(cfg)
 !
 !  One rank <-> one GPU; NCCL id is created on root and broadcast over MPI.
@@ -505,6 +547,11 @@ contains
 !  variable slots must be unchanged: pcb200_reconfigure refuses anything else), then rebuild the device constants.
 !
       call pcb200_fill_physics_pars_c(cfg)
+      cfg%Omega=Omega
+      if (lgrav) then
+        if (pcb200_fill_strat_pars_c(cfg)==0) call fatal_error('reload_GPU_config', &
+            'gpu_b200: the new gravity / heating / conduction set-up is not supported')
+      endif
       cfg%cdt=cdt; cfg%cdtv=cdtv; cfg%cdtv2=cdtv2; cfg%cdtv3=cdtv3; cfg%dtmax=dtmax
       call pcb200_reconfigure(cfg)
       call reload_gpu_config_c

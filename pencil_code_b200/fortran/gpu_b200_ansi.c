@@ -13,10 +13,16 @@
      density.f90:4591-4593          ldiff_hyper3lnrho(3) diffrho_hyper3(4) lupw_lnrho(5)
      hydro.f90:9367                 lupw_uu(2)
      entropy.f90:8675-8816          chi(1) lheatc_chiconst(18) lupw_ss(29) lviscosity_heat(141)
+     eos_idealgas.f90:4598-4599     cs2bot(10) cs2top(11)
+     gravity_simple.f90:1571-1609   gravz(1) gravx_xpencil(11) gravy_ypencil(13) enum_gravz_profile(20) z1(23) z2(24)
+     entropy.f90:8686-8864          FbotKbot(14) FtopKtop(15) widthss(31) luminosity(34) cool(36) wcool(43) cs2cool(53)
+                                    hcond0(72) hcond1(73) hcond2(76) lheatc_kprof(116) lcooling_general(132)
+                                    lcooling_to_cs2cool(133) lmultilayer(139) lhcond0_density_dep(156) lcalc_heat_cool(167)
    Module-procedure symbol names follow the compiler's mangling; the Makefile passes
    MODULE_PREFIX/INFIX/SUFFIX exactly as it does for the Astaroth glue (gfortran: __ , _MOD_ , "").
 */
 #include <stddef.h>
+#include <math.h>
 #include "headers_c.h"
 #include "pcb200.h"
 
@@ -36,6 +42,7 @@ extern void MODPROC(equationofstate, pushpars2c)(FINT8 *);
 extern void MODPROC(density, pushpars2c)(FINT8 *);
 extern void MODPROC(hydro, pushpars2c)(FINT8 *);
 extern void MODPROC(energy, pushpars2c)(FINT8 *);
+extern void MODPROC(gravity, pushpars2c)(FINT8 *);
 extern void MODPROC(forcing, forcing_pars_hel)(REAL *coef1, REAL *coef2, REAL *coef3, REAL *fda, REAL *kk,
                                                REAL *phase, REAL *fact);
 extern void MODPROC(forcing, pushpars2c)(FINT8 *);
@@ -79,6 +86,55 @@ void pcb200_fill_physics_pars_c(pcb200_config *c)
     c->eta = PD(p, 1); c->lresi_eta_const = PI_(p, 4); c->lupw_aa = PI_(p, 7); c->llorentzforce = PI_(p, 8);
     c->lohmic_heat = PI_(p, 105);
   }
+}
+
+/* Vertically stratified set-ups (lgrav): constant gravz, K-profile conduction, 'gaussian' cooling layer, the constants
+   of the 'c1' / 'cT' entropy boundary conditions.  Returns 0 when the configuration uses something else.
+   The profile selectors are string enums on the Fortran side (enum_gravz_profile, enum_cooling_profile are hashes of
+   the strings), so the supported case is recognised by its effect instead: gravx/gravy pencils all zero and
+   gravz_zpencil == gravz everywhere is what gravz_profile='const' produces (gravity_simple.f90:521-523). */
+int pcb200_fill_strat_pars_c(pcb200_config *c)
+{
+  static FINT8 p[NPAR_MAX];
+  int i;
+  const int mx = c->nx + 6, my = c->ny + 6, mz = c->nz + 6;
+
+  for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+  MODPROC(gravity, pushpars2c)(p);
+  c->gravz = PD(p, 1);
+  {
+    const REAL *gz = (const REAL *)p[1], *gx = (const REAL *)p[10], *gy = (const REAL *)p[12];
+    for (i = 0; i < mz; i++) if (gz[i] != (REAL)c->gravz) return 0;
+    for (i = 0; i < mx; i++) if (gx[i] != (REAL)0.) return 0;
+    for (i = 0; i < my; i++) if (gy[i] != (REAL)0.) return 0;
+  }
+  c->z1 = PD(p, 23); c->z2 = PD(p, 24);
+  if (PI_(p, 8) || PI_(p, 9)) return 0; /* lxyzdependence, lboussinesq_grav */
+
+  for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+  MODPROC(equationofstate, pushpars2c)(p);
+  c->cs2bot = PD(p, 10); c->cs2top = PD(p, 11);
+
+  c->lheatc_Kprof = 0; c->cool = 0.;
+  if (c->iss >= 0) {
+    for (i = 0; i < NPAR_MAX; i++) p[i] = 0;
+    MODPROC(energy, pushpars2c)(p);
+    c->lheatc_Kprof = PI_(p, 116);
+    c->hcond0 = PD(p, 72); c->hcond1 = PD(p, 73); c->hcond2 = PD(p, 76); c->widthss = PD(p, 31);
+    if (c->lheatc_Kprof && (!PI_(p, 139) || PI_(p, 156))) return 0; /* lmultilayer=T, lhcond0_density_dep=F */
+    if (c->lheatc_Kprof && c->hcond0 == 0.) c->lheatc_Kprof = 0;      /* entropy.f90:6139: nothing is added */
+    c->FbotKbot = PD(p, 14); c->FtopKtop = PD(p, 15);
+    if (PI_(p, 167)) {                                                /* lcalc_heat_cool */
+      if (PD(p, 34) != 0. || PI_(p, 132) || !PI_(p, 133)) return 0;   /* luminosity, lcooling_general, lcooling_to_cs2cool */
+      c->cool = PD(p, 36); c->wcool = PD(p, 43); c->cs2cool = PD(p, 53);
+      { /* cooling_profile='gaussian': profz_cool(n) = cool*exp(-0.5*((ztop-z)/wcool)^2) (entropy.f90:1323,1367) */
+        const REAL *pc = (const REAL *)p[20];
+        const double q = (c->ztop - c->z0) / c->wcool, want = c->cool * exp(-0.5 * q * q);
+        if (fabs((double)pc[0] - want) > 1e-6 * fabs(c->cool)) return 0;
+      }
+    }
+  }
+  return 1;
 }
 
 /* called by rhs_GPU before the last substep: draw the step's coefficients with the host RNG
