@@ -179,7 +179,10 @@ void update_after_substep_gpu_c(void);
 void load_farray_c(void);
 void copy_farray_c(double *f);
 void gpu_prepare_for_first_substep_c(double *t);
-/* gpu_astaroth.cc:1833-1849 copyVBApointers */
+/* gpu_astaroth.cc:1833-1849 copyVBApointers.  The device layout is the library's own (as the reference's VBA is
+   Astaroth's): x fastest, row pitch mx (+2 with one pad cell at either end for kernel variant 10), and with kernel
+   variant 10 and the entropy module the variables are stored as u, s, lnrho, A (lnrho and s exchanged);
+   load_farray_c / copy_farray_c translate to and from the Fortran f-array. */
 void get_farray_ptr_gpu_c(double **p_in, double **p_out);
 void reload_gpu_config_c(void);
 /* gpu_astaroth.cc:2179-2241 updateInConfig* ; return index>=0 or -1 if unknown */

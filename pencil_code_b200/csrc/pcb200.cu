@@ -257,7 +257,7 @@ __global__ void unpack_y(double *__restrict__ f, const double *__restrict__ buf,
 // ---------------------------------------------------------------------------
 constexpr int RED_THREADS = 256;
 
-template <bool ENT, bool MAG> __global__ void __launch_bounds__(RED_THREADS) cfl_kernel(const double *f, double *partial_max) {
+template <bool ENT, bool MAG, bool SW = false> __global__ void __launch_bounds__(RED_THREADS) cfl_kernel(const double *f, double *partial_max) {
   __shared__ double sm[RED_THREADS / 32];
   const long long ncell = (long long)cP.nx * cP.ny * cP.nz;
   double m = 0.0;
@@ -266,7 +266,7 @@ template <bool ENT, bool MAG> __global__ void __launch_bounds__(RED_THREADS) cfl
     const long long r = c / cP.nx;
     const int iy = (int)(r % cP.ny) + NG, iz = (int)(r / cP.ny) + NG;
     GlobalTaps tp{f + ix + cP.sy * iy + cP.sz * iz};
-    m = fmax(m, cfl_cell<ENT, MAG>(tp, iz - NG).dt1);
+    m = fmax(m, cfl_cell<ENT, MAG, GlobalTaps, SW>(tp, iz - NG).dt1);
   }
   m = warp_max(m);
   if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
@@ -296,7 +296,7 @@ __global__ void final_max(const double *partial, int n, double *out) {
 // dt = 1/dt1 (set_dt sub.f90:4223-4254)
 __global__ void dt_from_dt1(const double *dt1, double *dt) { dt[0] = 1.0 / dt1[0]; }
 
-template <bool ENT, bool MAG>
+template <bool ENT, bool MAG, bool SW = false>
 __global__ void __launch_bounds__(RED_THREADS) diag_kernel(const double *f, double *partial /*[grid][DS_NSUM+DM_NMAX]*/) {
   __shared__ double sm[RED_THREADS / 32][DS_NSUM + DM_NMAX];
   const long long ncell = (long long)cP.nx * cP.ny * cP.nz;
@@ -311,7 +311,7 @@ __global__ void __launch_bounds__(RED_THREADS) diag_kernel(const double *f, doub
     const int iy = (int)(r % cP.ny) + NG, iz = (int)(r / cP.ny) + NG;
     GlobalTaps tp{f + ix + cP.sy * iy + cP.sz * iz};
     double cs[DS_NSUM], cm[DM_NMAX];
-    diag_cell<ENT, MAG>(tp, cs, cm, iz - NG);
+    diag_cell<ENT, MAG, GlobalTaps, SW>(tp, cs, cm, iz - NG);
 #pragma unroll
     for (int i = 0; i < DS_NSUM; ++i) s[i] += cs[i];
 #pragma unroll
@@ -360,7 +360,7 @@ __device__ __forceinline__ double hash_noise(unsigned long long gx, unsigned lon
 }
 
 __global__ void init_synthetic_kernel(double *f, int ent, int mag, double x0, double y0, double z0, double dx, double dy,
-                                      double dz, int gx0, int gy0, int gz0, unsigned long long seed) {
+                                      double dz, int gx0, int gy0, int gz0, unsigned long long seed, int swap) {
   const long long ncell = (long long)cP.nx * cP.ny * cP.nz;
   const long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (c >= ncell) return;
@@ -381,8 +381,10 @@ __global__ void init_synthetic_kernel(double *f, int ent, int mag, double x0, do
     v[n++] = 0.01 * (sin(2 * x) + cos(2 * z));
     v[n++] = 0.01 * (sin(2 * y) + cos(2 * x));
   }
-  for (int k = 0; k < n; ++k)
-    f[o + k * cP.sv] = v[k] + 1e-3 * (hash_noise(gx0 + i, gy0 + j, gz0 + l, k, seed) - 0.5);
+  for (int k = 0; k < n; ++k) { // k: slot in registration order; swap: lnrho and s exchanged on the device
+    const int kd = (swap && k == 3) ? 4 : ((swap && k == 4) ? 3 : k);
+    f[o + kd * cP.sv] = v[k] + 1e-3 * (hash_noise(gx0 + i, gy0 + j, gz0 + l, k, seed) - 0.5);
+  }
 }
 
 // ---------------------------------------------------------------------------
@@ -453,7 +455,8 @@ struct State {
   CUtensorMap tmap_df;      // df tiles (32 x 8 x 1 x nvar) for L2 prefetch
   CUtensorMap tmap3_ring[2], tmap3_scal[2]; // variant 5: 3-variable and {lnrho,ss} boxes
   CUtensorMap tmap9[2];     // variant 9: one (38 x 14 x 1 x nvar) box per plane
-  CUtensorMap tmap10_i[2], tmap10_o1[2], tmap10_o3[2], tmap10_d1, tmap10_d3; // variant 10: interior boxes of f (in), clipped 1- and 3-variable boxes of f (out) and df
+  CUtensorMap tmap10_i[2], tmap10_ol[2], tmap10_on[2], tmap10_dl, tmap10_dn; // variant 10: interior boxes of f (in), clipped boxes of the late / immediate variable groups of f (out) and df
+  bool swap = false;        // variant 10 with entropy: lnrho and s exchange their slots on the device (Slots<ENT, true>)
   int variant = 1;          // kernel actually used (1 = global loads, 4 = TMA ring anisotropic, 5 = TMA ring isotropic, 9 = all-trail + TMEM)
   int nsm = 148;
   cudaStream_t stream = nullptr, comm_stream = nullptr;
@@ -800,7 +803,7 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v10(
   dim3 g(gx, gy, nch), b(V2_TX, V10_CTA / V2_TX, 1); // eight compute warps (+ the producer warpgroup)
   const int w = (a.fin == S.f[0]) ? 0 : 1;
   V10Maps tm;
-  tm.h = S.tmap9[w]; tm.i = S.tmap10_i[w]; tm.d1 = S.tmap10_d1; tm.d3 = S.tmap10_d3; tm.o1 = S.tmap10_o1[w ^ 1]; tm.o3 = S.tmap10_o3[w ^ 1];
+  tm.h = S.tmap9[w]; tm.i = S.tmap10_i[w]; tm.dl = S.tmap10_dl; tm.dn = S.tmap10_dn; tm.ol = S.tmap10_ol[w ^ 1]; tm.on = S.tmap10_on[w ^ 1];
   rhs_update_v10<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(tm, v);
 }
 
@@ -1018,10 +1021,12 @@ static void update_ghosts(double *f, cudaStream_t st) {
 }
 
 template <bool ENT, bool MAG> static void launch_cfl_t(const double *f, cudaStream_t st) {
-  cfl_kernel<ENT, MAG><<<S.red_blocks, RED_THREADS, 0, st>>>(f, S.partial);
+  if (ENT && S.swap) cfl_kernel<ENT, MAG, ENT><<<S.red_blocks, RED_THREADS, 0, st>>>(f, S.partial);
+  else cfl_kernel<ENT, MAG><<<S.red_blocks, RED_THREADS, 0, st>>>(f, S.partial);
 }
 template <bool ENT, bool MAG> static void launch_diag_t(const double *f, cudaStream_t st) {
-  diag_kernel<ENT, MAG><<<S.red_blocks, RED_THREADS, 0, st>>>(f, S.partial);
+  if (ENT && S.swap) diag_kernel<ENT, MAG, ENT><<<S.red_blocks, RED_THREADS, 0, st>>>(f, S.partial);
+  else diag_kernel<ENT, MAG><<<S.red_blocks, RED_THREADS, 0, st>>>(f, S.partial);
 }
 
 // Courant dt of the step (equ.f90:408 -> sub.f90:4223): dt1 max over all cells and ranks
@@ -1330,7 +1335,7 @@ extern "C" void pcb200_init_synthetic(const int *seed) {
   const long long n = (long long)P.nx * P.ny * P.nz;
   init_synthetic_kernel<<<(unsigned)((n + 255) / 256), 256, 0, S.stream>>>(
       S.f[S.cur], S.cfg.iss >= 0, S.cfg.iax >= 0, S.cfg.x0, S.cfg.y0, S.cfg.z0, S.cfg.dx, S.cfg.dy, S.cfg.dz,
-      S.cfg.ipx * S.cfg.nx, S.cfg.ipy * S.cfg.ny, S.cfg.ipz * S.cfg.nz, (unsigned long long)*seed);
+      S.cfg.ipx * S.cfg.nx, S.cfg.ipy * S.cfg.ny, S.cfg.ipz * S.cfg.nz, (unsigned long long)*seed, S.swap ? 1 : 0);
   CK(cudaGetLastError());
   S.launches++;
   update_ghosts(S.f[S.cur], S.stream);
@@ -1358,6 +1363,7 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
     S.variant = kv ? kv : (tma_ok && !strat ? (iso ? 10 : 4) : 1);
     if (S.variant >= 5 && !iso) S.variant = 4; // anisotropic spacing: same kernel structure with per-direction weights
     S.xpad = S.variant == 10 ? 1 : 0;
+    S.swap = S.variant == 10 && S.cfg.iss >= 0;
   }
   CK(cudaMalloc(&S.zprof_dev, sizeof(double) * 3 * S.cfg.nz));
   derive_pars();
@@ -1402,14 +1408,15 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
     for (int w = 0; w < 2; ++w) make_tensor_map(&S.tmap9[w], S.f[w], V2_HX, V2_HY, P.nvar);
   }
   if (S.variant == 10) { // tensor maps over the ALLOCATIONS: x coordinates are physical (logical + 1)
+    const int nlate = v10_nlate(S.cfg.iss >= 0, S.cfg.iax >= 0);
     for (int w = 0; w < 2; ++w) {
       make_tensor_map(&S.tmap9[w], S.f_alloc[w], V10_HX, V2_HY, P.nvar);
       make_tensor_map(&S.tmap10_i[w], S.f_alloc[w], V2_TX, V2_TY, P.nvar);
-      make_tensor_map(&S.tmap10_o1[w], S.f_alloc[w], V2_TX, V2_TY, 1, true);
-      make_tensor_map(&S.tmap10_o3[w], S.f_alloc[w], V2_TX, V2_TY, 3, true);
+      make_tensor_map(&S.tmap10_ol[w], S.f_alloc[w], V2_TX, V2_TY, nlate, true);
+      make_tensor_map(&S.tmap10_on[w], S.f_alloc[w], V2_TX, V2_TY, P.nvar - nlate, true);
     }
-    make_tensor_map(&S.tmap10_d1, S.df_alloc, V2_TX, V2_TY, 1, true);
-    make_tensor_map(&S.tmap10_d3, S.df_alloc, V2_TX, V2_TY, 3, true);
+    make_tensor_map(&S.tmap10_dl, S.df_alloc, V2_TX, V2_TY, nlate, true);
+    make_tensor_map(&S.tmap10_dn, S.df_alloc, V2_TX, V2_TY, P.nvar - nlate, true);
   }
   if (S.variant == 5) {
     for (int w = 0; w < 2; ++w) {
@@ -1484,7 +1491,29 @@ extern "C" void finalize_gpu_c(void) {
 FTN_ALIAS(finalize_gpu_c)
 
 // host f-array (rows of mx doubles, contiguous) <-> device buffer (row pitch P.sy): `rows` rows from row `row0`
+static void copy_rows(double *dev, double *host, size_t row0, size_t rows, cudaMemcpyKind kind, cudaStream_t st);
+// the same for a row range in HOST variable order when lnrho and s are exchanged on the device (State::swap)
+static void copy_rows_host_order(double *dev, double *host, size_t row0, size_t rows, cudaMemcpyKind kind, cudaStream_t st) {
+  const size_t per_var = (size_t)S.P.my * S.P.mz;
+  size_t r = row0;
+  const size_t end = row0 + rows;
+  while (r < end) {
+    const size_t k = r / per_var, stop = std::min(end, (k + 1) * per_var), n = stop - r;
+    const size_t kd = (k == 3) ? 4 : (k == 4 ? 3 : k); // device slot of host variable k
+    const long long shift = ((long long)kd - (long long)k) * (long long)per_var; // rows between the two
+    // copy_rows addresses both sides by the same row index: present shifted base pointers for this piece
+    copy_rows(dev + shift * S.P.sy, host, r, n, kind, st);
+    r = stop;
+  }
+}
+static bool g_in_swap = false;
 static void copy_rows(double *dev, double *host, size_t row0, size_t rows, cudaMemcpyKind kind, cudaStream_t st) {
+  if (S.swap && !g_in_swap) {
+    g_in_swap = true;
+    copy_rows_host_order(dev, host, row0, rows, kind, st);
+    g_in_swap = false;
+    return;
+  }
   const Pars &P = S.P;
   double *d = dev + row0 * P.sy, *h = host + row0 * P.mx;
   if (P.sy == P.mx) {
@@ -1789,6 +1818,7 @@ extern "C" __attribute__((alias("update_on_gpu_arr_by_ind_c"))) void update_on_g
 // gpu_astaroth_ansi.c pos_real_ptr_c: address of variable slot `ind` inside a device f-array
 extern "C" void *pos_real_ptr_c(void **ptr, int *ind) {
   need_init("pos_real_ptr_c");
-  return (void *)((double *)(*ptr) + (size_t)(*ind) * S.P.sv);
+  const int k = *ind, kd = (S.swap && k == 3) ? 4 : ((S.swap && k == 4) ? 3 : k); // registration order -> device slot
+  return (void *)((double *)(*ptr) + (size_t)kd * S.P.sv);
 }
 extern "C" __attribute__((alias("pos_real_ptr_c"))) void *pos_real_ptr_c_(void **, int *);

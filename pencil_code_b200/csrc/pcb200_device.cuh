@@ -128,8 +128,12 @@ struct GlobalTaps {
 };
 
 // variable slots in Pencil Code's registration order (register.f90:135-147)
-template <bool ENT> struct Slots {
-  static constexpr int IUX = 0, ILN = 3, ISS = 4, IAX = ENT ? 5 : 4;
+// SW (kernel variant 10 with entropy): on the DEVICE the slots of lnrho and s are exchanged (u, s, lnrho, A), so that the
+// variables the fused kernel finishes three planes late (u, and s with a magnetic field) and the ones it finishes at once
+// (lnrho, A; s without a magnetic field) are neighbours and move as ONE TMA box per array and stage each
+// (pcb200.cu: State::swap; host <-> device copies permute the two variables, copy_rows)
+template <bool ENT, bool SW = false> struct Slots {
+  static constexpr int IUX = 0, ILN = (ENT && SW) ? 4 : 3, ISS = SW ? 3 : 4, IAX = ENT ? 5 : 4;
 };
 
 __device__ __forceinline__ int pair_of(int i, int j) { // 0=xy 1=yz 2=zx
@@ -381,8 +385,8 @@ struct CflParts {
   double dt1, advec_uu, advec_cs2, advec_va2, diffus_chi;
 };
 // n: interior z index of the cell (K-profile conduction only)
-template <bool ENT, bool MAG, class T> __device__ __forceinline__ CflParts cfl_cell(const T &tp, int n) {
-  typedef Slots<ENT> S;
+template <bool ENT, bool MAG, class T, bool SW = false> __device__ __forceinline__ CflParts cfl_cell(const T &tp, int n) {
+  typedef Slots<ENT, SW> S;
   const Pars &P = cP;
   CflParts r;
   const double u0 = tp.val(S::IUX), u1 = tp.val(S::IUX + 1), u2 = tp.val(S::IUX + 2);
@@ -426,9 +430,9 @@ template <bool ENT, bool MAG, class T> __device__ __forceinline__ CflParts cfl_c
 enum { DS_U2 = 0, DS_RHO, DS_OU, DS_EPSK, DS_SS, DS_B2, DS_J2, DS_AB, DS_JB, DS_NSUM };
 enum { DM_U2 = 0, DM_B2, DM_J2, DM_DTU, DM_DTC, DM_DTB, DM_DTNU, DM_DTCHI, DM_NMAX };
 
-template <bool ENT, bool MAG, class T>
+template <bool ENT, bool MAG, class T, bool SW = false>
 __device__ __forceinline__ void diag_cell(const T &tp, double *__restrict__ sums, double *__restrict__ maxs, int n) {
-  typedef Slots<ENT> S;
+  typedef Slots<ENT, SW> S;
   const Pars &P = cP;
   double u[3], uij[3][3];
 #pragma unroll
@@ -483,7 +487,7 @@ __device__ __forceinline__ void diag_cell(const T &tp, double *__restrict__ sums
     maxs[DM_B2] = b2;
     maxs[DM_J2] = jsq;
   }
-  const CflParts c = cfl_cell<ENT, MAG>(tp, n);
+  const CflParts c = cfl_cell<ENT, MAG, T, SW>(tp, n);
   maxs[DM_DTCHI] = c.diffus_chi / P.cdtv;
   maxs[DM_DTU] = c.advec_uu / P.cdt;
   maxs[DM_DTC] = sqrt(c.advec_cs2) / P.cdt;

@@ -18,7 +18,11 @@
 //     issues that stage's stores, refills the ring slots the stage released and requests df one stage ahead.  A TMA
 //     instruction costs its issuing warp 30-60 ns (measured: 26 of them per stage by a compute warp made the kernel
 //     60 % slower), so they must not sit in a compute warp; 196 registers per thread leave room for the extra warp.
-//     Variables that share a plane are moved as one box: u (3, late), lnrho, s (late with a magnetic field), A (3).
+//     Variables that share a plane are moved as ONE box per array: on the device this variant stores the variables as
+//     u, s, lnrho, A (Slots<ENT, true>), so the ones finished three planes late (u; s with a magnetic field) and the ones
+//     finished at once (lnrho, A) are neighbours: 2 instead of 4 TMA operations per array and stage (measured: substep 2
+//     9.6 -> 8.75 ms at 512^3; a TMA operation on a 2 KB box costs the engine as much as one on a 16 KB box,
+//     profiles/r02_tma_rate.txt).
 #pragma once
 #include "pcb200_v9.cuh"
 
@@ -96,13 +100,16 @@ __device__ __forceinline__ double v10_dxy(const double *q) {
 extern __shared__ __align__(1024) double v10_smem[];
 
 // (x coordinates are physical) tm_h: f_in, box 40 x 14 x 1 x NV (halo'd planes); tm_i: f_in, box 32 x 8 x 1 x NV (interior boxes);
-// tm_d1/tm_d3: df, boxes 32 x 8 x 1 x {1,3}; tm_o1/tm_o3: f_out likewise -- these four end at the last interior cell in x and y
+// dl/dn: df, boxes 32 x 8 x 1 x {variables finished late, variables finished at once}; ol/on: f_out likewise -- these four end
+// at the last interior cell in x and y
 struct V10Maps {
-  CUtensorMap h, i, d1, d3, o1, o3;
+  CUtensorMap h, i, dl, dn, ol, on;
 };
+// device slots of this variant: u, [s,] lnrho, [A] (Slots<ENT, true>); the first v10_nlate() of them are finished three planes late
+__host__ __device__ constexpr int v10_nlate(bool ent, bool mag) { return 3 + ((ent && mag) ? 1 : 0); }
 template <bool ENT, bool MAG, bool HYP, bool UPW>
 __global__ void __launch_bounds__(V10_CTA, 1) rhs_update_v10(const __grid_constant__ V10Maps tm, const __grid_constant__ V10Args a) {
-  typedef Slots<ENT> S;
+  typedef Slots<ENT, true> S;
   constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
   constexpr int NGRP = MAG ? 2 : 1;   // vector fields with a grad div: u (and A)
   constexpr bool SDEL = ENT && MAG;   // ds/dt contains the Ohmic heating -> finalised three planes late as well
@@ -169,13 +176,13 @@ __global__ void __launch_bounds__(V10_CTA, 1) rhs_update_v10(const __grid_consta
     mbar_expect_tx(&ibar[si], L::ITX);
     tma_load_4d(iring + si * L::ISLOT, &tm.i, &ibar[si], bx0 + NG + 1, by0 + NG, zc0 + j, 0);
   };
-  // variable groups that share a plane: g = 0: u (late), 1: lnrho, 2: s (late with a magnetic field), 3: A
-  constexpr int NGR = 2 + (ENT ? 1 : 0) + (MAG ? 1 : 0);
+  // variable groups that share a plane: g = 0: the NLATE leading slots (u, and s with a magnetic field), finished three
+  // planes late; g = 1: the others (lnrho, A; s without a magnetic field), finished at once.  One box per group and array.
+  constexpr int NGR = 2, NLATE = v10_nlate(ENT, MAG);
   auto group = [&](int j, int g, int &k0, int &nv, int &plane) { // -> does stage j update this group?
-    if (!ENT && g >= 2) g = 3; // without entropy the third group is A
-    const bool del = g == 0 || (SDEL && g == 2);
-    k0 = g == 0 ? S::IUX : (g == 1 ? S::ILN : (g == 2 ? S::ISS : S::IAX));
-    nv = (g == 0 || g == 3) ? 3 : 1;
+    const bool del = g == 0;
+    k0 = del ? 0 : NLATE;
+    nv = del ? NLATE : NV - NLATE;
     plane = zc0 - NG + j - (del ? NG : 0);
     return del ? (j >= 2 * NG) : (j >= NG && j < nst - NG);
   };
@@ -185,8 +192,8 @@ __global__ void __launch_bounds__(V10_CTA, 1) rhs_update_v10(const __grid_consta
     for (int g = 0; g < NGR; ++g) {
       int k0, nv, pl;
       if (!group(j, g, k0, nv, pl) || (PCB200_ABL & 8)) continue;
-      tma_store_4d(nv == 3 ? &tm.o3 : &tm.o1, iring + (j % V10_NI) * L::ISLOT + k0 * V2_THREADS, bx0 + NG + 1, by0 + NG, pl, k0);
-      if (a.write_df) tma_store_4d(nv == 3 ? &tm.d3 : &tm.d1, dstg + b * L::STG + k0 * V2_THREADS, bx0 + NG + 1, by0 + NG, pl, k0);
+      tma_store_4d(g == 0 ? &tm.ol : &tm.on, iring + (j % V10_NI) * L::ISLOT + k0 * V2_THREADS, bx0 + NG + 1, by0 + NG, pl, k0);
+      if (a.write_df) tma_store_4d(g == 0 ? &tm.dl : &tm.dn, dstg + b * L::STG + k0 * V2_THREADS, bx0 + NG + 1, by0 + NG, pl, k0);
     }
     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
   };
@@ -204,7 +211,7 @@ __global__ void __launch_bounds__(V10_CTA, 1) rhs_update_v10(const __grid_consta
 #pragma unroll 1
       for (int g = 0; g < NGR; ++g)
         if (group(j, g, k0, nv, pl))
-          tma_load_4d(dstg + b * L::STG + k0 * V2_THREADS, nv == 3 ? &tm.d3 : &tm.d1, &dbar[b], bx0 + NG + 1, by0 + NG, pl, k0);
+          tma_load_4d(dstg + b * L::STG + k0 * V2_THREADS, g == 0 ? &tm.dl : &tm.dn, &dbar[b], bx0 + NG + 1, by0 + NG, pl, k0);
     }
   };
   auto produce = [&](int j) { // top of stage j >= 1 (every compute warp has finished stage j - 1), by one lane

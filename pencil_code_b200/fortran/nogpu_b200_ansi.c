@@ -19,6 +19,7 @@ void pcb200_hand_dt1_to_set_dt_c(void) { not_in_start("pcb200_hand_dt1_to_set_dt
 int pcb200_forcing_supported_c(const int *nx, const int *my, const int *mz) { (void)nx; (void)my; (void)mz; return 1; }
 int pcb200_sizeof_config(void) { return (int)sizeof(pcb200_config); }
 void pcb200_fill_physics_pars_c(pcb200_config *cfg) { (void)cfg; }
+int pcb200_fill_strat_pars_c(pcb200_config *cfg) { (void)cfg; return 1; }
 void pcb200_push_forcing_c(void) {}
 void pcb200_set_dt(const double *dt, const int *ldt) { (void)dt; (void)ldt; }
 void pcb200_get_dt(double *dt) { (void)dt; not_in_start("pcb200_get_dt"); }
