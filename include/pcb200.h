@@ -200,6 +200,23 @@ void test_bcs_c(void);
    CPU boundary conditions on a randomised mesh by more than 1e-12 relative (0 = passed); does not exit */
 long long pcb200_test_bcs(void);
 
+/* No counterpart in the reference: added for callers that cannot call
+   cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+   Courant reduction of a device f-array WITHOUT any allocation: dt1_max_dev[0] = max over all interior cells of this rank
+   of the inverse time step (equ.f90:1858-1972, the quantity pcb200_get_dt1_max returns after substep 1 of a Courant
+   step, before the reduction over ranks), computed by the same kernels; the per-block partial maxima live in a
+   file-scope static __device__ array of PCB200_NOALLOC_MAX_BLOCKS doubles (32 KB, held by every GPU that loads the
+   library until exit) instead of cudaMalloc'ed scratch.
+     f_dev        device f-array in the library's layout with valid ghost zones (get_farray_ptr_gpu_c, first pointer)
+     dt1_max_dev  device pointer to one double (output)
+     nblocks      size of the reduction grid = number of scratch slots used, 1..PCB200_NOALLOC_MAX_BLOCKS
+   Work is queued on the library's stream (pcb200_set_stream); no host synchronisation, no cudaMalloc/cudaFree.
+   Returns 0, or prints the reason to stderr and returns 1 (nblocks beyond the maximum or < 1), 2 (not initialized),
+   3 (null argument), 4 (scratch address unavailable), 5 (launch failed).  All calls share the scratch array, which
+   keeps the last call's contents (nothing in it needs clearing); calls that overlap on the GPU race on it. */
+#define PCB200_NOALLOC_MAX_BLOCKS 4096
+int pcb200_dt1_max_noalloc(const double *f_dev, double *dt1_max_dev, const int *nblocks);
+
 /* gpu.h:12 n_gpu_reduced_vars=20.  Slot layout of dst[]: */
 enum {
   PCB200_RED_URMS = 0, PCB200_RED_UMAX, PCB200_RED_RHOM, PCB200_RED_BRMS, PCB200_RED_BMAX,

@@ -1822,3 +1822,61 @@ extern "C" void *pos_real_ptr_c(void **ptr, int *ind) {
   return (void *)((double *)(*ptr) + (size_t)kd * S.P.sv);
 }
 extern "C" __attribute__((alias("pos_real_ptr_c"))) void *pos_real_ptr_c_(void **, int *);
+
+// ===========================================================================
+// Courant reduction without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// Same two kernels as compute_dt (cfl_kernel -> final_max), but the per-block partial maxima go to a file-scope
+// device array instead of the cudaMalloc'ed State::partial.  Every GPU that loads the library holds the array
+// (PCB200_NOALLOC_MAX_BLOCKS doubles = 32 KB) until exit.  All calls share it and it keeps the last call's contents;
+// nothing in it has to start at zero (every block 0..nblocks-1 overwrites its own slot before final_max reads exactly
+// those slots), so it is not cleared.  Calls that overlap on the GPU (different streams) race on it.
+// ===========================================================================
+static __device__ __align__(256) double g_noalloc_partial[PCB200_NOALLOC_MAX_BLOCKS];
+
+// In host code `g_noalloc_partial` is only the host-side stand-in of the symbol: its device address is asked for once
+// per device, with that device current, and cached.
+static double *noalloc_scratch_ptr() {
+  static double *ptr[64] = {nullptr};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  if (!ptr[dev]) {
+    double *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_noalloc_partial);
+    if (e != cudaSuccess) {
+      std::fprintf(stderr, "pcb200_dt1_max_noalloc: cudaGetSymbolAddress failed: %s\n", cudaGetErrorString(e));
+      return nullptr;
+    }
+    ptr[dev] = p;
+  }
+  return ptr[dev];
+}
+
+template <bool ENT, bool MAG> static void launch_cfl_into(const double *f, double *partial, int nblocks, cudaStream_t st) {
+  if (ENT && S.swap) cfl_kernel<ENT, MAG, ENT><<<nblocks, RED_THREADS, 0, st>>>(f, partial);
+  else cfl_kernel<ENT, MAG><<<nblocks, RED_THREADS, 0, st>>>(f, partial);
+}
+
+extern "C" int pcb200_dt1_max_noalloc(const double *f_dev, double *dt1_max_dev, const int *nblocks) {
+  if (!S.initialized) { std::fprintf(stderr, "pcb200_dt1_max_noalloc: called before initialize_gpu_c\n"); return 2; }
+  if (!f_dev || !dt1_max_dev || !nblocks) { std::fprintf(stderr, "pcb200_dt1_max_noalloc: null argument\n"); return 3; }
+  const int nb = *nblocks;
+  if (nb < 1 || nb > PCB200_NOALLOC_MAX_BLOCKS) {
+    std::fprintf(stderr, "pcb200_dt1_max_noalloc: nblocks=%d outside 1..%d (size of the static scratch array)\n", nb,
+                 (int)PCB200_NOALLOC_MAX_BLOCKS);
+    return 1;
+  }
+  double *scratch = noalloc_scratch_ptr();
+  if (!scratch) return 4;
+  cudaStream_t st = S.stream;
+  const bool ent = S.cfg.iss >= 0, mag = S.cfg.iax >= 0;
+  if (ent && mag) launch_cfl_into<true, true>(f_dev, scratch, nb, st);
+  else if (ent) launch_cfl_into<true, false>(f_dev, scratch, nb, st);
+  else if (mag) launch_cfl_into<false, true>(f_dev, scratch, nb, st);
+  else launch_cfl_into<false, false>(f_dev, scratch, nb, st);
+  final_max<<<1, 256, 0, st>>>(scratch, nb, dt1_max_dev);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { std::fprintf(stderr, "pcb200_dt1_max_noalloc: launch failed: %s\n", cudaGetErrorString(e)); return 5; }
+  S.launches += 2;
+  return 0;
+}

@@ -76,7 +76,7 @@ ABI_SYMBOLS = (
     "get_farray_ptr_gpu_c", "reload_gpu_config_c", "update_on_gpu_scal_by_name_c", "update_on_gpu_vec_by_name_c",
     "update_on_gpu_arr_by_name_c", "update_on_gpu_scal_by_ind_c", "update_on_gpu_vec_by_ind_c",
     "update_on_gpu_arr_by_ind_c", "pos_real_ptr_c", "split_update_gpu_c", "radtransfer_gpu_c", "test_bcs_c",
-    "get_gpu_reduced_vars_c", "pcb200_driver_run", "pcb200_test_bcs",
+    "get_gpu_reduced_vars_c", "pcb200_driver_run", "pcb200_test_bcs", "pcb200_dt1_max_noalloc",
 )
 # the reference binds these with a trailing underscore (FTNIZE, src/headers_c.h:31-37)
 FTN_SYMBOLS = tuple(s + "_" for s in ABI_SYMBOLS if s.endswith("_c"))
@@ -132,6 +132,8 @@ def load_library():
     L.pcb200_driver_run.argtypes = [C.POINTER(DriverState), C.c_int, dp, C.c_int]
     L.pcb200_driver_run.restype = C.c_int
     L.pcb200_test_bcs.restype = C.c_longlong
+    L.pcb200_dt1_max_noalloc.argtypes = [C.c_void_p, C.c_void_p, ip]
+    L.pcb200_dt1_max_noalloc.restype = C.c_int
     L.pcb200_reconfigure.argtypes = [C.POINTER(Config)]
     L.pos_real_ptr_c.argtypes = [C.POINTER(C.c_void_p), ip]
     L.pos_real_ptr_c.restype = C.c_void_p
