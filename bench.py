@@ -252,7 +252,7 @@ def main():
     g.L.pcb200_set_stream(stream.cuda_stream)
     g.register_GPU()
     g.initialize_GPU(fh, nt=0)
-    if world > 1 and args.halo == "p2p" and npz > 1:
+    if world > 1 and args.halo == "p2p":
         blobs = [None] * world  # CUDA IPC handles of every rank's f buffers: z halos become copy-engine puts over NVLink
         dist.all_gather_object(blobs, g.p2p_export())
         ok = torch.tensor([1 if g.p2p_connect(blobs) else 0], device=dev)
@@ -390,7 +390,7 @@ def main():
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": config_dict(args, world, wname, nvar, nbytes_f),
-            "z_halo": ("none (1 GPU)" if world == 1 else ("peer puts over NVLink (copy engines)" if args.halo == "p2p" and npz > 1 else "NCCL send/recv")),
+            "z_halo": ("none (1 GPU)" if world == 1 else ("peer puts over NVLink (copy engines)" + (", y faces as strided peer puts" if npy > 1 else "") if args.halo == "p2p" else "NCCL send/recv")),
             "kernel_variant": args.kernel_variant, "finite": finite, "checksum": checksum,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nbytes_f * world,
                     "d2h_bytes_per_step": nbytes_f * world, "steps": args.e2e_steps,

@@ -128,8 +128,9 @@ void pcb200_set_stream(void *cuda_stream);
 /* z-halo exchange as copy-engine "puts" into the neighbours' ghost planes over NVLink peer memory (CUDA IPC),
    replacing the NCCL send/recv pair (and with it mpicomm.f90:1544-2271 for the z direction) without using SMs:
    every rank exports one blob after initialize_gpu_c, the host all-gathers them (MPI_Allgather in gpu_b200.f90)
-   and every rank connects with the table of all ranks' blobs (rank order).  Optional: without these calls the
-   z exchange runs on NCCL.  Ranks must not call finalize_gpu_c before all ranks have finished stepping. */
+   and every rank connects with the table of all ranks' blobs (rank order).  With yz-pencils (nprocy > 1) the y faces
+   travel the same way: one strided 2-D copy per side into the y neighbour's ghost rows (no pack/unpack kernels;
+   load_farray_c keeps the two-sided exchange).  Optional: without these calls all exchanges run on NCCL.  Ranks must not call finalize_gpu_c before all ranks have finished stepping. */
 int pcb200_p2p_blob_bytes(void);
 void pcb200_p2p_export(unsigned char *blob);
 /* returns 0 when both z neighbours' buffers are mapped, 1 when they cannot be (peer GPU not visible, no P2P) */

@@ -475,8 +475,13 @@ struct State {
   cudaEvent_t ev_snap = nullptr, ev_d2h = nullptr;
   bool d2h_pending = false;
   bool p2p = false;
+  bool p2p_y = false;        // y faces of yz-pencils as strided copy-engine puts as well (put_y)
+  bool in_load = false;      // load_farray_c in progress: the y exchange stays two-sided (NCCL), see exchange_y
+  double *peer_fy[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}}; // [0 = lower (y-) neighbour, 1 = upper][buffer]
+  unsigned long long *peer_flags_y[2] = {nullptr, nullptr};         // the y neighbours' flag arrays (slots 2, 3 are the y arrivals)
+  unsigned long long seq_y = 0;
   double *peer_f[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}}; // [0 = lower (z-) neighbour, 1 = upper][buffer]
-  unsigned long long *flags = nullptr;                               // device: [0] written by the lower neighbour, [1] by the upper
+  unsigned long long *flags = nullptr;                               // device: [0] written by the lower z neighbour, [1] by the upper; [2], [3] likewise for y
   unsigned long long *peer_flags[2] = {nullptr, nullptr};            // the neighbours' flag pairs
   unsigned long long *seq_slots = nullptr;                           // device ring of sequence numbers (copy sources)
   unsigned long long seq = 0;                                        // exchanges started so far (identical on all ranks)
@@ -938,8 +943,34 @@ static void exchange_z(double *f, cudaStream_t st) {
   if (!S.loopback) NCK(nccl.GroupEnd());
 }
 
+// y faces of yz-pencils as copy-engine puts over NVLink peer memory (mpicomm.f90:1604-1731 sends the same rows): the 3
+// top interior rows of every plane go straight into the lower ghost rows of the upper y neighbour and vice versa --
+// ONE strided 2-D copy per side (width 3 rows, one line per (variable, plane), pitch = one plane), no pack / unpack
+// kernels, no SM.  z-ghost planes travel along (stale there); the z exchange that follows rewrites them, y ghosts included.
+// Then the y arrival counters; the stream waits for both neighbours' rows before anything reads the y ghosts.
+// One-sided writes are safe for the reason given at put_z: a neighbour that has finished substep n has consumed my
+// output of substep n-1, so my kernel that last READ the buffer it now writes into has finished.
+static void put_y(double *f, cudaStream_t st) {
+  const Pars &P = S.P;
+  const int b = (f == S.f[0]) ? 0 : 1;
+  const size_t pitch = (size_t)P.sz * sizeof(double), width = (size_t)NG * P.sy * sizeof(double), lines = (size_t)P.mz * P.nvar;
+  CK(cudaMemcpy2DAsync(S.peer_fy[1][b], pitch, f + (size_t)P.ny * P.sy, pitch, width, lines, cudaMemcpyDeviceToDevice, st));
+  CK(cudaMemcpy2DAsync(S.peer_fy[0][b] + (size_t)(NG + P.ny) * P.sy, pitch, f + (size_t)NG * P.sy, pitch, width, lines, cudaMemcpyDeviceToDevice, st));
+  S.seq_y++;
+  unsigned long long *slot = S.seq_slots + 16 + (S.seq_y & 15);
+  if (drv_write64((CUstream)st, (CUdeviceptr)slot, (cuuint64_t)S.seq_y, 0) != CUDA_SUCCESS) die("cuStreamWriteValue64 failed");
+  CK(cudaMemcpyAsync(S.peer_flags_y[1] + 2, slot, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st)); // I am its lower y neighbour
+  CK(cudaMemcpyAsync(S.peer_flags_y[0] + 3, slot, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st)); // I am its upper y neighbour
+  for (int d = 2; d < 4; ++d)
+    if (drv_wait64((CUstream)st, (CUdeviceptr)(S.flags + d), (cuuint64_t)S.seq_y, CU_STREAM_WAIT_VALUE_GEQ) != CUDA_SUCCESS)
+      die("cuStreamWaitValue64 failed");
+}
+
 // y-face exchange (yz-pencils): pack 3 rows x nz planes x mx, send/recv, unpack
 static void exchange_y(double *f, cudaStream_t st) {
+  // load_farray_c copies whole planes, y-ghost rows included: a neighbour's put could land before the tail of my upload
+  // and be overwritten by it -- the upload path therefore keeps the two-sided exchange (both ranks have uploaded)
+  if (S.p2p_y && !S.in_load) { put_y(f, st); return; }
   const Pars &P = S.P;
   const int up = rank_of(S.cfg.ipy + 1, S.cfg.ipz), dn = rank_of(S.cfg.ipy - 1, S.cfg.ipz);
   const size_t cnt = S.ybuf_doubles;
@@ -1255,9 +1286,9 @@ extern "C" int pcb200_p2p_blob_bytes(void) { return 3 * (int)sizeof(cudaIpcMemHa
 extern "C" void pcb200_p2p_export(unsigned char *blob) {
   need_init("pcb200_p2p_export");
   if (!S.flags) {
-    CK(cudaMalloc(&S.flags, 2 * sizeof(unsigned long long)));
-    CK(cudaMemset(S.flags, 0, 2 * sizeof(unsigned long long)));
-    CK(cudaMalloc(&S.seq_slots, 16 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&S.flags, 4 * sizeof(unsigned long long)));
+    CK(cudaMemset(S.flags, 0, 4 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&S.seq_slots, 32 * sizeof(unsigned long long)));
     SYNC_DEVICE();
   }
   cudaIpcMemHandle_t h[3];
@@ -1269,39 +1300,60 @@ extern "C" void pcb200_p2p_export(unsigned char *blob) {
 extern "C" int pcb200_p2p_connect(const unsigned char *blobs, const int *nranks) {
   need_init("pcb200_p2p_connect");
   if (*nranks != S.nranks) die("pcb200_p2p_connect: %d blobs for %d ranks", *nranks, S.nranks);
-  if (S.cfg.nprocz < 2) return 0; // z is wrapped locally
+  if (S.cfg.nprocz < 2 && S.cfg.nprocy < 2) return 0; // everything is wrapped locally
   if (!S.flags) die("pcb200_p2p_connect: call pcb200_p2p_export first");
   load_stream_memops();
-  const int nb[2] = {rank_of(S.cfg.ipy, S.cfg.ipz - 1), rank_of(S.cfg.ipy, S.cfg.ipz + 1)};
-  for (int d = 0; d < 2; ++d) {
-    if (d == 1 && nb[1] == nb[0]) { // two slabs: the same neighbour on both sides
-      S.peer_f[1][0] = S.peer_f[0][0]; S.peer_f[1][1] = S.peer_f[0][1]; S.peer_flags[1] = S.peer_flags[0];
-      break;
-    }
+  // every neighbour's buffers are mapped once per process, whatever number of sides it is the neighbour on
+  struct Mapped { int rank; double *f[2]; unsigned long long *flags; };
+  std::vector<Mapped> mapped;
+  auto map_rank = [&](int r, Mapped &out) -> bool {
+    for (const Mapped &m : mapped)
+      if (m.rank == r) { out = m; return true; }
     cudaIpcMemHandle_t h[3];
-    std::memcpy(h, blobs + (size_t)nb[d] * sizeof(h), sizeof(h));
+    std::memcpy(h, blobs + (size_t)r * sizeof(h), sizeof(h));
     void *p[3];
     for (int i = 0; i < 3; ++i) {
       const cudaError_t e = cudaIpcOpenMemHandle(&p[i], h[i], cudaIpcMemLazyEnablePeerAccess);
       if (e != cudaSuccess) { // e.g. the neighbour's GPU is not visible to this process: the caller keeps NCCL
-        std::fprintf(stderr, "pcb200: rank %d cannot map rank %d's buffers (%s); z halo stays on NCCL\n", S.rank, nb[d], cudaGetErrorString(e));
+        std::fprintf(stderr, "pcb200: rank %d cannot map rank %d's buffers (%s); halos stay on NCCL\n", S.rank, r, cudaGetErrorString(e));
         (void)cudaGetLastError();
-        return 1;
+        return false;
       }
       S.ipc_opened.push_back(p[i]);
     }
-    S.peer_f[d][0] = (double *)p[0] + S.xpad; S.peer_f[d][1] = (double *)p[1] + S.xpad; S.peer_flags[d] = (unsigned long long *)p[2];
+    out.rank = r; out.f[0] = (double *)p[0] + S.xpad; out.f[1] = (double *)p[1] + S.xpad; out.flags = (unsigned long long *)p[2];
+    mapped.push_back(out);
+    return true;
+  };
+  if (S.cfg.nprocz >= 2) {
+    const int nb[2] = {rank_of(S.cfg.ipy, S.cfg.ipz - 1), rank_of(S.cfg.ipy, S.cfg.ipz + 1)};
+    for (int d = 0; d < 2; ++d) {
+      Mapped m;
+      if (!map_rank(nb[d], m)) return 1;
+      S.peer_f[d][0] = m.f[0]; S.peer_f[d][1] = m.f[1]; S.peer_flags[d] = m.flags;
+    }
+  }
+  if (S.cfg.nprocy >= 2) {
+    const int nb[2] = {rank_of(S.cfg.ipy - 1, S.cfg.ipz), rank_of(S.cfg.ipy + 1, S.cfg.ipz)};
+    for (int d = 0; d < 2; ++d) {
+      Mapped m;
+      if (!map_rank(nb[d], m)) return 1;
+      S.peer_fy[d][0] = m.f[0]; S.peer_fy[d][1] = m.f[1]; S.peer_flags_y[d] = m.flags;
+    }
   }
   return 0;
 }
-// switch the z halo to peer puts; call on ALL ranks, and only after every rank's pcb200_p2p_connect returned 0
+// switch the halos to peer puts; call on ALL ranks, and only after every rank's pcb200_p2p_connect returned 0
 extern "C" void pcb200_p2p_enable(void) {
   need_init("pcb200_p2p_enable");
-  if (S.cfg.nprocz < 2) return;
-  if (!S.peer_f[0][0] || !S.peer_f[1][0]) die("pcb200_p2p_enable: not connected");
+  if (S.cfg.nprocz < 2 && S.cfg.nprocy < 2) return;
+  if (S.cfg.nprocz >= 2 && (!S.peer_f[0][0] || !S.peer_f[1][0])) die("pcb200_p2p_enable: not connected");
+  if (S.cfg.nprocy >= 2 && (!S.peer_fy[0][0] || !S.peer_fy[1][0])) die("pcb200_p2p_enable: not connected (y)");
   wait_halo(S.stream); // an exchange started on the NCCL path finishes there
   SYNC_STREAM((S.stream));
-  S.p2p = true;
+  S.p2p = S.cfg.nprocz >= 2;
+  static const char *noy = std::getenv("PCB200_P2P_NO_Y"); // lab switch: y faces stay on pack + NCCL + unpack
+  S.p2p_y = S.cfg.nprocy >= 2 && !(noy && std::atoi(noy) != 0);
 }
 
 extern "C" void pcb200_set_stream(void *cuda_stream) {
@@ -1430,11 +1482,14 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   const char *lp = std::getenv("PCB200_LOOPBACK_P2P"); // test hook: the peer-put z halo with this rank as both neighbours
   if (S.loopback && lp && std::atoi(lp) != 0) {
     load_stream_memops();
-    CK(cudaMalloc(&S.flags, 2 * sizeof(unsigned long long)));
-    CK(cudaMemset(S.flags, 0, 2 * sizeof(unsigned long long)));
-    CK(cudaMalloc(&S.seq_slots, 16 * sizeof(unsigned long long)));
-    for (int d = 0; d < 2; ++d) { S.peer_f[d][0] = S.f[0]; S.peer_f[d][1] = S.f[1]; S.peer_flags[d] = S.flags; }
-    S.p2p = true;
+    CK(cudaMalloc(&S.flags, 4 * sizeof(unsigned long long)));
+    CK(cudaMemset(S.flags, 0, 4 * sizeof(unsigned long long)));
+    CK(cudaMalloc(&S.seq_slots, 32 * sizeof(unsigned long long)));
+    for (int d = 0; d < 2; ++d) {
+      S.peer_f[d][0] = S.f[0]; S.peer_f[d][1] = S.f[1]; S.peer_flags[d] = S.flags;
+      S.peer_fy[d][0] = S.f[0]; S.peer_fy[d][1] = S.f[1]; S.peer_flags_y[d] = S.flags;
+    }
+    S.p2p = true; S.p2p_y = true;
   }
   if (S.cfg.nprocy > 1 || S.loopback) {
     S.ybuf_doubles = (size_t)NG * P.mx * P.nz * P.nvar;
@@ -1539,7 +1594,9 @@ extern "C" void load_farray_c(void) {
   } else {
     copy_rows(S.f[S.cur], S.host_f, 0, (size_t)S.P.my * S.P.mz * S.P.nvar, cudaMemcpyHostToDevice, S.stream);
   }
+  S.in_load = true;
   update_ghosts(S.f[S.cur], S.stream);
+  S.in_load = false;
   SYNC_STREAM((S.stream));
 }
 FTN_ALIAS(load_farray_c)

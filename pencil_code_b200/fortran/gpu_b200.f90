@@ -196,7 +196,7 @@ module GPU
   integer :: kernel_variant=0      !PAR-DOC: 0=auto (9 on isotropic grids, else 4; 1 for odd mx), 1=global-load kernel, 4/5/9=TMA z-marching kernels (include/pcb200.h)
   integer :: gpu_device=-1         !PAR-DOC: CUDA device; -1 = local rank modulo device count
 
-  logical :: lp2p_halo=.true.      !PAR-DOC: z halos as peer-memory puts over NVLink (else NCCL send/recv)
+  logical :: lp2p_halo=.true.      !PAR-DOC: z halos and y faces as peer-memory puts over NVLink (else NCCL send/recv)
   namelist /gpu_run_pars/ ltest_bcs, ltest_rhs, it_test_rhs, kernel_variant, gpu_device, lp2p_halo
 
   type(pcb200_config), save :: cfg
@@ -333,7 +333,7 @@ contains
 !  the CUDA IPC handles of its device buffers, the table of all ranks is all-gathered over MPI.
 !  (All ranks of the run share one 8-GPU box; without this block the z exchange stays on NCCL.)
 !
-      if (ncpus>1 .and. nprocz>1 .and. lp2p_halo) call connect_p2p_halo
+      if (ncpus>1 .and. (nprocz>1.or.nprocy>1) .and. lp2p_halo) call connect_p2p_halo
       if (nt>0) call load_farray_to_GPU(f)
       call get_farray_ptr_gpu
 

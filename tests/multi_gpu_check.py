@@ -31,7 +31,7 @@ def run_case(rank, world, npy, npz, variant, ldt, p2p, nsteps=3):
     g = GPU(cfg, nccl=(ids[0], rank, world))
     g.register_GPU()
     g.initialize_GPU(f)
-    if p2p and npz > 1:  # z halos as copy-engine puts into the neighbours' ghost planes (CUDA IPC) instead of NCCL
+    if p2p:  # z halos (and y faces of pencils) as copy-engine puts into the neighbours' ghost zones (CUDA IPC) instead of NCCL
         blobs = [None] * world
         dist.all_gather_object(blobs, g.p2p_export())
         oks = [None] * world
@@ -68,7 +68,7 @@ def run_case(rank, world, npy, npz, variant, ldt, p2p, nsteps=3):
         derr = max(abs(a[k] - b[k]) / max(abs(b[k]), 1e-300) for a, b in zip(series, sc) for k in ("urms", "brms", "jrms", "rhom"))
         ok = err <= 1e-11 and derr <= 1e-11 and abs(dt - dtc) <= 1e-12 * dtc
         print("case %dx%d variant %d ldt %d %s: rel Linf %.2e  diag %.2e  dt %.3e/%.3e  %s" %
-              (npy, npz, variant, ldt, "p2p" if (p2p and npz > 1) else "nccl", err, derr, dt, dtc, "ok" if ok else "FAIL"), flush=True)
+              (npy, npz, variant, ldt, "p2p" if p2p else "nccl", err, derr, dt, dtc, "ok" if ok else "FAIL"), flush=True)
     flag = [ok]
     dist.broadcast_object_list(flag, src=0)
     return flag[0]
@@ -81,7 +81,8 @@ def main():
     dist.init_process_group("gloo")
     cases = [(1, world, 10, False, True), (1, world, 5, True, True), (1, world, 10, True, False), (1, world, 9, True, True)]
     if world % 2 == 0:
-        cases += [(2, world // 2, 10, True, True), (2, world // 2, 4, False, False), (world, 1, 1, False, False), (world, 1, 10, True, False)]
+        cases += [(2, world // 2, 10, True, True), (2, world // 2, 4, False, False), (world, 1, 1, False, False), (world, 1, 10, True, False),
+                  (world, 1, 10, False, True), (2, world // 2, 9, False, True)]
     ok = True
     for npy, npz, variant, ldt, p2p in cases:
         ok = run_case(rank, world, npy, npz, variant, ldt, p2p) and ok
