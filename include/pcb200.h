@@ -62,10 +62,11 @@ typedef struct pcb200_config {
   int lperi[3];
   /* device selection: -1 = local rank modulo device count */
   int device;
-  /* kernel selection: 0 = auto (fastest validated: 5 on isotropic grids, 4 otherwise, 1 when mx is odd),
-     1 = global-load kernel, 2 = TMA/shared-memory z-marching kernel, 3 = 2 with the physics split over two warp
-     roles, 4 = 2 with lead/trail z-mixed derivatives, 5 = 4 specialised for dx=dy=dz, 6 / 7 = 5 with
-     the z histories of the scalars / of all variables in tensor memory, 8 = 7 with 12 warps on a (32 x 12) tile */
+  /* kernel selection: 0 = auto (10 on isotropic grids with even mx, 4 on anisotropic ones, 1 when mx is odd or the run is
+     vertically stratified), 1 = global-load kernel (also the stratified one), 4 = TMA/shared-memory z-marching kernel with
+     lead/trail z-mixed derivatives and per-direction weights, 5 = 4 specialised for dx=dy=dz (round-1 default, kept as an
+     independent cross-check), 10 = all global traffic through the TMA engine, z histories and all-trail accumulators in
+     tensor memory.  Other numbers (earlier lab variants 2, 3, 6-9) are refused. */
   int kernel_variant;
   /* ---- vertically stratified set-ups (samples/conv-slab); all zero = triply periodic box --------------------
      z boundary condition per [bottom/top][variable slot] when lperi[2]=0 (boundcond.f90:1421-1787, bcz12):

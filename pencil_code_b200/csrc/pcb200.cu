@@ -454,10 +454,10 @@ struct State {
   CUtensorMap tmap[2];      // TMA descriptors of f[0], f[1] (kernel variant 2)
   CUtensorMap tmap_df;      // df tiles (32 x 8 x 1 x nvar) for L2 prefetch
   CUtensorMap tmap3_ring[2], tmap3_scal[2]; // variant 5: 3-variable and {lnrho,ss} boxes
-  CUtensorMap tmap9[2];     // variant 9: one (38 x 14 x 1 x nvar) box per plane
+  CUtensorMap tmap9[2];     // variant 10: one halo'd (40 x 14 x 1 x nvar) box per plane
   CUtensorMap tmap10_i[2], tmap10_ol[2], tmap10_on[2], tmap10_dl, tmap10_dn; // variant 10: interior boxes of f (in), clipped boxes of the late / immediate variable groups of f (out) and df
   bool swap = false;        // variant 10 with entropy: lnrho and s exchange their slots on the device (Slots<ENT, true>)
-  int variant = 1;          // kernel actually used (1 = global loads, 4 = TMA ring anisotropic, 5 = TMA ring isotropic, 9 = all-trail + TMEM)
+  int variant = 1;          // kernel actually used (1 = global loads, 4 = TMA ring anisotropic, 5 = TMA ring isotropic, 10 = all-trail + TMEM + TMA for all global traffic)
   int nsm = 148;
   cudaStream_t stream = nullptr, comm_stream = nullptr;
   bool own_stream = false;
@@ -732,46 +732,6 @@ template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v5(c
   rhs_update_v5<ENT, MAG, HYP, UPW, 0><<<g, b, L::SMEM_BYTES, st>>>(S.tmap3_ring[w], S.tmap3_scal[w], v);
 }
 
-template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v9(const UpdateArgs &a, cudaStream_t st) {
-  constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
-  typedef V9Layout<NV> L;
-  static bool attr_set = false;
-  if (!attr_set) {
-    CK(cudaFuncSetAttribute(rhs_update_v9<ENT, MAG, HYP, UPW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L::SMEM_BYTES));
-    attr_set = true;
-  }
-  V9Args v;
-  v.fin = a.fin; v.dt_dev = a.dt_dev; v.alpha = a.alpha; v.beta = a.beta;
-  v.read_df = a.read_df; v.write_df = a.write_df; v.z_lo = a.z_lo; v.z_hi = a.z_hi; v.frc = a.frc;
-  for (int k = 0; k < MAXVAR; ++k) {
-    const bool del = k < 3 || (ENT && MAG && k == 4); // finalised three planes late (pcb200_v9.cuh)
-    const long long off = (long long)std::min(k, NV - 1) * S.P.sv - (del ? NG * S.P.sz : 0);
-    v.df_k[k] = a.df + off;
-    v.fo_k[k] = a.fout + off;
-  }
-  const int gx = (S.P.nx + V2_TX - 1) / V2_TX, gy = (S.P.ny + V2_TY - 1) / V2_TY;
-  const int nzr = a.z_hi - a.z_lo;
-  // one CTA per SM; every z chunk pays 6 extra stages (3 warm-up + 3 cool-down, each ~1/4 of an evaluated plane):
-  // among the chunk counts that give at least one full wave take the one with the best (wave fill) x (chunk efficiency)
-  int pick = 1;
-  {
-    double best = 0.0;
-    const int tiles = gx * gy;
-    const int cmax = std::max(1, nzr / 8);
-    for (int c = 1; c <= cmax && tiles * c <= 16 * S.nsm; ++c) {
-      const int lz = (nzr + c - 1) / c;
-      const double waves = (double)tiles * ((nzr + lz - 1) / lz) / S.nsm;
-      const double eff = waves / std::ceil(waves) * (lz / (lz + 1.5));
-      if (eff > best + 0.01) { best = eff; pick = c; }
-    }
-  }
-  v.lz = (nzr + pick - 1) / pick;
-  const int nch = (nzr + v.lz - 1) / v.lz;
-  dim3 g(gx, gy, nch), b(V2_TX, V2_TY, 1);
-  const int w = (a.fin == S.f[0]) ? 0 : 1;
-  rhs_update_v9<ENT, MAG, HYP, UPW><<<g, b, L::SMEM_BYTES, st>>>(S.tmap9[w], v);
-}
-
 template <bool ENT, bool MAG, bool HYP, bool UPW> static void launch_update_v10(const UpdateArgs &a, cudaStream_t st) {
   constexpr int NV = 4 + (ENT ? 1 : 0) + (MAG ? 3 : 0);
   typedef V10Layout<NV> L;
@@ -831,7 +791,6 @@ static void launch_update(const UpdateArgs &a, cudaStream_t st) {
 #define DISPATCH(E, M, H, U)                                   \
   do {                                                         \
     if (S.variant == 10) launch_update_v10<E, M, H, U>(a, st); \
-    else if (S.variant == 9) launch_update_v9<E, M, H, U>(a, st); \
     else if (S.variant == 5) launch_update_v5<E, M, H, U>(a, st);   \
     else if (S.variant == 4) launch_update_v2<E, M, H, U, true>(a, st); \
     else launch_update_v1<E, M, H, U>(a, st);                  \
@@ -1408,7 +1367,7 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   { // kernel variant (decides the device layout): TMA needs 16-byte global strides -> mx even
     const bool tma_ok = ((S.cfg.nx + 2 * NG) % 2 == 0);
     const int kv = S.cfg.kernel_variant;
-    if (kv != 0 && kv != 1 && kv != 4 && kv != 5 && kv != 9 && kv != 10) die("kernel_variant=%d unknown (0 = auto, 1, 4, 5, 9, 10)", kv);
+    if (kv != 0 && kv != 1 && kv != 4 && kv != 5 && kv != 10) die("kernel_variant=%d unknown (0 = auto, 1, 4, 5, 10)", kv);
     if (kv >= 2 && !tma_ok) die("kernel_variant=%d needs an even mx=nx+6 (TMA stride alignment)", kv);
     const bool iso = S.cfg.dx == S.cfg.dy && S.cfg.dy == S.cfg.dz; // variants >= 5 share one set of stencil weights
     const bool strat = !S.cfg.lperi[2] || S.cfg.gravz != 0.0 || S.cfg.Omega != 0.0 || S.cfg.lheatc_Kprof || S.cfg.cool != 0.0;
@@ -1455,9 +1414,6 @@ extern "C" void initialize_gpu_c(double *f, int *comm_fint, double *t, int *nt, 
   if (S.variant == 4) {
     make_tensor_map(&S.tmap[0], S.f[0]);
     make_tensor_map(&S.tmap[1], S.f[1]);
-  }
-  if (S.variant == 9) {
-    for (int w = 0; w < 2; ++w) make_tensor_map(&S.tmap9[w], S.f[w], V2_HX, V2_HY, P.nvar);
   }
   if (S.variant == 10) { // tensor maps over the ALLOCATIONS: x coordinates are physical (logical + 1)
     const int nlate = v10_nlate(S.cfg.iss >= 0, S.cfg.iax >= 0);

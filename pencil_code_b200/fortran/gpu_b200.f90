@@ -193,7 +193,7 @@ module GPU
   logical :: ltest_bcs=.false.     !PAR-DOC: accepted for namelist compatibility with gpu_astaroth
   logical :: ltest_rhs=.false.     !PAR-DOC: run test_rhs_gpu (equ.f90:1974-2143) at step it_test_rhs
   integer :: it_test_rhs=1
-  integer :: kernel_variant=0      !PAR-DOC: 0=auto (9 on isotropic grids, else 4; 1 for odd mx), 1=global-load kernel, 4/5/9=TMA z-marching kernels (include/pcb200.h)
+  integer :: kernel_variant=0      !PAR-DOC: 0=auto (10 on isotropic grids, else 4; 1 for odd mx or stratified runs), 1=global-load kernel, 4/5/10=TMA z-marching kernels (include/pcb200.h)
   integer :: gpu_device=-1         !PAR-DOC: CUDA device; -1 = local rank modulo device count
 
   logical :: lp2p_halo=.true.      !PAR-DOC: z halos and y faces as peer-memory puts over NVLink (else NCCL send/recv)

@@ -33,7 +33,7 @@ def _cfg(name, **over):
     return c
 
 
-VARIANTS = [1, 4, 5, 9, 10]
+VARIANTS = [1, 4, 5, 10]
 
 
 @pytest.mark.parametrize("variant", VARIANTS)
@@ -50,14 +50,14 @@ def test_one_substep(oracle_mod, name, variant):
     assert err.max() <= TOL_SUBSTEP, (name, variant, err)
 
 
-@pytest.mark.parametrize("variant", [4, 5, 9, 10])
+@pytest.mark.parametrize("variant", [4, 5, 10])
 @pytest.mark.parametrize("shape", [(32, 8, 4), (64, 16, 40), (70, 9, 5), (6, 6, 6), (34, 10, 17), (40, 24, 3), (32, 8, 100)])
 def test_tma_variants_tile_edges(oracle_mod, shape, variant):
     """grids that are not multiples of the 32x8 tile, shorter than one tile, the minimum nz = 3, and z-chunk remainders"""
     nx, ny, nz = shape
     cfg = pcfg.make_config(nx, True, True, ny=ny, nz=nz, nu=5e-3, eta=4e-3, chi=3e-3, cdt=0.4, cdtv=0.3)
     cfg.update(dx=0.2, dy=0.21, dz=0.19)
-    if variant >= 5:  # variants 5 and 9 are isotropic-spacing specialisations (anisotropic grids fall back to 4)
+    if variant >= 5:  # variants 5 and 10 are isotropic-spacing specialisations (anisotropic grids fall back to 4)
         cfg.update(dx=0.2, dy=0.2, dz=0.2)
     fg, fc, _, _, _ = pu.run_both(cfg, oracle_mod, 0, dt=0.01, substeps_only=3, kernel_variant=variant)
     assert pu.rel_linf(fg, fc).max() <= 5e-12, (shape, variant)
