@@ -38,6 +38,12 @@ def run_case(rank, world, npy, npz, variant, ldt, p2p, nsteps=3):
         dist.all_gather_object(oks, g.p2p_connect(blobs))
         assert all(oks), "peer mapping failed on some rank: %s" % oks
         g.p2p_enable()
+        # the Fortran order (connect_p2p_halo and p2p_enable come before load_farray_to_GPU): upload again with the host's ghost
+        # zones poisoned -- a neighbour's put that lands before the tail of my upload must not be overwritten by stale host ghosts
+        f[:, :3] = np.nan; f[:, -3:] = np.nan
+        f[:, :, :3] = np.nan; f[:, :, -3:] = np.nan
+        f[:, :, :, :3] = np.nan; f[:, :, :, -3:] = np.nan
+        g.load_farray_to_GPU(f)
     dt, t = (0.0 if ldt else pcfg.fixed_dt(gcfg)), 0.0
     series = []
     for s in range(nsteps):
