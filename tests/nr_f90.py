@@ -8,7 +8,16 @@ driven with the reference's own forcing stream.
                         put(2)==0 -> `dummy = mars_ran(put(1))`, i.e. initialise and discard one number);
 * gaunoise_vect      -- initcond.f90:5005-5047: per (n, m) row and per variable pair one vector r(mx), one vector p(mx),
                         sin branch for the 1st and 3rd component, cos branch (same r, p) for the 2nd; ghosts included;
-* helical_forcing_draw -- forcing.f90:1804-1815 (fran(2): phase, wavevector index) and :1909 (phi), in that order.
+* helical_forcing_draw -- forcing.f90:1804-1815 (fran(2): phase, wavevector index) and :1909 (phi), in that order;
+* Ran0               -- general.f90:867-889 `ran0` (random_gen='min_std', the default: general.f90:86), state = the single
+                        seed integer set by `random_seed_wrapper(PUT=...)` (general.f90:817-821), negative seeds included
+                        (Fortran integer division truncates toward zero);
+* power_randomphase_hel -- initcond.f90:5772-6653 for the arguments magnetic.f90:2326-2331 passes by default (3-D vector
+                        potential, no cutoff, no Gaussian, lscale_tobox=T, projection on, nfact=4, lfactors=F, no random
+                        amplitudes): per-processor random phases in the processor's block of k-space (draw order of
+                        random_number_wrapper_3, general.f90:722-768: first index outermost), broken power law, solenoidal
+                        projection, unnormalised backward FFT (fourier_fftpack.f90:3561-3710: cfftb, natural
+                        index order) -- here one numpy FFT of the global array.
 """
 import math
 
@@ -94,3 +103,58 @@ def helical_forcing_draw(rng, nk):
     ik = int(nk * (0.9999 * fran2) + 1)
     phi = rng.next() * 2 * math.pi
     return phase, ik - 1, phi
+
+
+MASK = 123459876
+
+
+def _tdiv(a, b):
+    q = abs(a) // abs(b)
+    return q if (a >= 0) == (b >= 0) else -q
+
+
+class Ran0:
+    def __init__(self, seed):
+        self.s = seed  # rstate(1)
+        self.am = 1.0 / float(IM)
+
+    def next(self):
+        d = _i32(self.s ^ MASK)
+        k = _tdiv(d, IQ)
+        d = _i32(IA * (d - k * IQ) - IR * k)
+        if d < 0:
+            d = _i32(d + IM)
+        r = self.am * d
+        self.s = _i32(d ^ MASK)
+        return r
+
+
+def power_randomphase_hel(make_rng, n, nprocy, nprocz, ampl, initpower, initpower2, kpeak, relhel, nfact=4.0):
+    """-> A[3][z][y][x] on the global n^3 grid.  make_rng(iproc) returns the generator of processor iproc as start.x seeds it
+    (start.f90:389: seed = -(10 + iproc)); iproc = ipy + nprocy*ipz (nprocx = 1)."""
+    nx, ny, nz = n, n // nprocy, n // nprocz
+    U = np.zeros((3, n, n, n), dtype=complex)  # [component][kz][ky][kx]
+    for iproc in range(nprocy * nprocz):
+        ipy, ipz = iproc % nprocy, iproc // nprocy
+        rng = make_rng(iproc)
+        for c in range(3):
+            r = np.array([rng.next() for _ in range(nx * ny * nz)]).reshape(nx, ny, nz)  # do i; do j; do k: a(i,j,k)
+            ph = math.pi * (2 * r - 1)
+            blk = ampl * (np.cos(ph) + 1j * np.sin(ph))
+            U[c, ipz * nz:(ipz + 1) * nz, ipy * ny:(ipy + 1) * ny, :] = blk.transpose(2, 1, 0)
+    kk = np.roll(np.arange(n) - n // 2, n // 2).astype(float)  # cshift((/(i-n/2,i=0,n-1)/), n/2)
+    KZ, KY, KX = np.meshgrid(kk, kk, kk, indexing="ij")
+    k2 = KX ** 2 + KY ** 2 + KZ ** 2
+    k2[0, 0, 0] = 1.0  # "avoid division by zero"
+    mhalf = .25 * (initpower - 3 + 1)
+    nexp1, nexp2 = .25 * nfact * (initpower - initpower2), 1. / nfact
+    kpeak1, kpeak21 = 1. / kpeak, 1. / kpeak ** 2
+    fact = (kpeak1 * 1.0) ** 1.5  # scale_factor = 1 (lscale_tobox=T), D1 = 0, D2 = 1
+    fact *= kpeak1                # lvectorpotential
+    U *= fact * ((k2 * kpeak21) ** mhalf) / (1. + (k2 * kpeak21) ** nexp1) ** nexp2
+    kdotu = (KX * U[0] + KY * U[1] + KZ * U[2]) / k2  # projection: v_i = u_i - k_i k_j u_j / k^2
+    U[0] -= KX * kdotu
+    U[1] -= KY * kdotu
+    U[2] -= KZ * kdotu
+    assert relhel == 0.0, "helical part (initcond.f90:6459-6530) not restated: samples/decay-reconnection has relhel_aa=0"
+    return np.fft.ifftn(U, axes=(1, 2, 3)).real * float(n) ** 3
