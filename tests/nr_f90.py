@@ -17,7 +17,9 @@ driven with the reference's own forcing stream.
                         amplitudes): per-processor random phases in the processor's block of k-space (draw order of
                         random_number_wrapper_3, general.f90:722-768: first index outermost), broken power law, solenoidal
                         projection, unnormalised backward FFT (fourier_fftpack.f90:3561-3710: cfftb, natural
-                        index order) -- here one numpy FFT of the global array.
+                        index order) -- here one numpy FFT of the global array;
+* ran0_stream, gaunoise_vect_decomposed -- the same generator vectorised, and gaunoise_vect as a run on several processors
+                        draws it (every processor its local array from its own seed).
 """
 import math
 
@@ -158,3 +160,36 @@ def power_randomphase_hel(make_rng, n, nprocy, nprocz, ampl, initpower, initpowe
     U[2] -= KZ * kdotu
     assert relhel == 0.0, "helical part (initcond.f90:6459-6530) not restated: samples/decay-reconnection has relhel_aa=0"
     return np.fft.ifftn(U, axes=(1, 2, 3)).real * float(n) ** 3
+
+
+def ran0_stream(seed, count):
+    """The first `count` numbers of Ran0(seed) as an array.  With the mask applied on the way in and out, ran0 is the plain
+    Lehmer sequence d_{n+1} = 16807 d_n mod (2^31 - 1) (Schrage's method is exact for positive d), so after the first number
+    (scalar routine: the seed may be negative) the sequence is built by doubling: d[k:2k] = 16807^k d[0:k]."""
+    r0 = Ran0(seed)
+    r0.next()
+    d = np.empty(count, dtype=np.uint64)
+    d[0] = r0.s ^ MASK
+    k, g = 1, IA
+    while k < count:
+        m = min(k, count - k)
+        d[k:k + m] = (d[:m] * np.uint64(g)) % np.uint64(IM)
+        g = (g * g) % IM
+        k *= 2
+    return d.astype(np.float64) * (1.0 / float(IM))
+
+
+def gaunoise_vect_decomposed(f, i1, ampl, nprocy, nprocz):
+    """gaunoise_vect (initcond.f90:5005-5047) for the three variables i1..i1+2 of a run on nprocy x nprocz processors with the
+    default generator: processor iproc = ipy + nprocy*ipz draws its LOCAL array (ghost rows and planes included, they are
+    overwritten by the boundary exchange) from Ran0(-(10 + iproc)) (start.f90:389).  f is the global array (nvar, mz, my, mx)."""
+    _, mzg, myg, mx = f.shape
+    ny, nz = (myg - 6) // nprocy, (mzg - 6) // nprocz
+    my, mz = ny + 6, nz + 6
+    for iproc in range(nprocy * nprocz):
+        ipy, ipz = iproc % nprocy, iproc // nprocy
+        u = ran0_stream(-(10 + iproc), mz * my * 4 * mx).reshape(mz, my, 4, mx)  # per (n, m): r, p for (1st, 2nd), r, p for 3rd
+        a1, a2 = np.sqrt(-2 * np.log(u[:, :, 0])), np.sqrt(-2 * np.log(u[:, :, 2]))
+        loc = np.stack([a1 * np.sin(2 * math.pi * u[:, :, 1]), a1 * np.cos(2 * math.pi * u[:, :, 1]),
+                        a2 * np.sin(2 * math.pi * u[:, :, 3])])
+        f[i1:i1 + 3, 3 + ipz * nz:3 + (ipz + 1) * nz, 3 + ipy * ny:3 + (ipy + 1) * ny, :] += ampl * loc[:, 3:-3, 3:-3, :]
