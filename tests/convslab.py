@@ -17,7 +17,9 @@ NG = 3
 COLUMNS = ("it", "t", "dt", "urms", "umax", "rhom", "ssm", "dtc", "dtu", "dtnu", "dtchi")
 
 
-def config(n=32, **over):
+def config(n=32, cp=1.0, **over):
+    """cp = 2 is samples/conv-slab_cp_2 (cp doubled, hcond0 doubled: the reference holds the SAME series for it, with ssm/cp
+    in place of ssm -- its check that nothing assumes cp = 1)."""
     cs0, gamma, rho0 = .57735, 1.6666666, 1.0
     Lx = Ly = 1.0
     Lz = 2.0
@@ -26,8 +28,7 @@ def config(n=32, **over):
     dx, dy, dz = Lx / n, Ly / n, Lz / (n - 1)
     gravz, z1, z2, zref = -1.0, 0.0, 1.0, 1.32
     mpoly0, mpoly1, mpoly2 = 1.0, 3.0, 0.0
-    hcond0 = 8e-3
-    cp = 1.0
+    hcond0 = 8e-3 * cp
     gamma_m1 = gamma - 1.0
     hcond1 = (mpoly1 + 1.) / (mpoly0 + 1.)  # entropy.f90:849-850
     hcond2 = (mpoly2 + 1.) / (mpoly0 + 1.)

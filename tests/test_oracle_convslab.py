@@ -42,12 +42,17 @@ def check_rows(rows, tol_scale=1.0):
     return worst
 
 
-def test_convslab_41_steps_match_the_reference_double_precision_series(oracle_mod):
-    c = convslab.config()
+@pytest.mark.parametrize("cp", [1.0, 2.0])
+def test_convslab_41_steps_match_the_reference_double_precision_series(oracle_mod, cp):
+    """cp = 2: samples/conv-slab_cp_2/reference.out.double -- the same 41 rows digit for digit (checked by
+    tests/golden/make_convslab_golden.py), its entropy column being ssbycpm = ssm/cp."""
+    c = convslab.config(cp=cp)
     f = convslab.initial_condition(c)
     o = oracle_mod.Oracle(c)
     df = np.zeros_like(f)
     rows = run_series(lambda dt, t, want: o.time_step(f, df, True, dt, t, diag=want))
+    for r in rows:
+        r["ssm"] /= cp
     check_rows(rows)
 
 
