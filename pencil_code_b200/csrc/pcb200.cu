@@ -471,6 +471,7 @@ struct State {
   // and then bumps the neighbour's counter, the receiver waits for the counter with a stream memory operation.
   bool host_registered = false; // the retained host f-array was page-locked by this library (cudaHostRegister)
   double *snap = nullptr;       // device snapshot of f for the asynchronous device-to-host copy
+  double *stage = nullptr;      // linear device image of the host f-array (nreal doubles): staging buffer of load_farray_c / copy_farray_c
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_snap = nullptr, ev_d2h = nullptr;
   bool d2h_pending = false;
@@ -1483,6 +1484,7 @@ extern "C" void finalize_gpu_c(void) {
   S.ev_pool.clear();
   if (S.host_registered && S.host_f) cudaHostUnregister(S.host_f);
   if (S.snap) cudaFree(S.snap);
+  if (S.stage) cudaFree(S.stage);
   if (S.copy_stream) { cudaStreamDestroy(S.copy_stream); cudaEventDestroy(S.ev_snap); cudaEventDestroy(S.ev_d2h); }
   for (void *q : S.ipc_opened) cudaIpcCloseMemHandle(q);
   S.ipc_opened.clear();
@@ -1518,6 +1520,24 @@ static void copy_rows_host_order(double *dev, double *host, size_t row0, size_t 
   }
 }
 static bool g_in_swap = false;
+// Padded device rows (variant 10: pitch mx+2) make the host<->device transfer a 2-D copy of 4 KB rows, which the copy engine
+// moves over PCIe at ~42 GB/s instead of the ~54 GB/s of one linear transfer (measured at 512^3: 2 x 8.9 GB per end-to-end step,
+// 475 instead of 360 ms).  load_farray_c / copy_farray_c of single-domain runs therefore go through a linear device image of
+// the host array (State::stage, allocated on first use): ONE linear PCIe transfer plus a repacking kernel on the device
+// (2 x 8.9 GB at HBM speed, ~7 ms).  PCB200_STAGED_COPY=0 restores the direct 2-D copies.
+static bool g_stage = false; // set around the copies of load_farray_c / copy_farray_c
+static bool staged_copy_enabled() {
+  static int on = -1;
+  if (on < 0) { const char *e = std::getenv("PCB200_STAGED_COPY"); on = e ? (std::atoi(e) != 0 ? 1 : 0) : 1; }
+  return on == 1;
+}
+__global__ void repack_rows_kernel(double *dst, size_t dpitch, const double *src, size_t spitch, int width, size_t rows) {
+  for (size_t r = blockIdx.x; r < rows; r += gridDim.x) {
+    const double *sr = src + r * spitch;
+    double *dr = dst + r * dpitch;
+    for (int x = threadIdx.x; x < width; x += blockDim.x) dr[x] = sr[x];
+  }
+}
 static void copy_rows(double *dev, double *host, size_t row0, size_t rows, cudaMemcpyKind kind, cudaStream_t st) {
   if (S.swap && !g_in_swap) {
     g_in_swap = true;
@@ -1527,9 +1547,24 @@ static void copy_rows(double *dev, double *host, size_t row0, size_t rows, cudaM
   }
   const Pars &P = S.P;
   double *d = dev + row0 * P.sy, *h = host + row0 * P.mx;
+  const size_t bytes = rows * P.mx * sizeof(double);
   if (P.sy == P.mx) {
     if (kind == cudaMemcpyHostToDevice) CK(cudaMemcpyAsync(d, h, rows * P.mx * sizeof(double), kind, st));
     else CK(cudaMemcpyAsync(h, d, rows * P.mx * sizeof(double), kind, st));
+  } else if (g_stage && bytes >= (1u << 20) && (row0 + rows) * P.mx <= S.nreal && staged_copy_enabled()) {
+    if (!S.stage) CK(cudaMalloc(&S.stage, S.nreal * sizeof(double)));
+    double *sg = S.stage + row0 * P.mx; // the host rows' own place in the linear image
+    const unsigned grid = (unsigned)std::min<size_t>(rows, (size_t)148 * 32);
+    if (kind == cudaMemcpyHostToDevice) {
+      CK(cudaMemcpyAsync(sg, h, bytes, kind, st));
+      repack_rows_kernel<<<grid, 256, 0, st>>>(d, (size_t)P.sy, sg, (size_t)P.mx, P.mx, rows);
+      CK(cudaGetLastError());
+    } else {
+      repack_rows_kernel<<<grid, 256, 0, st>>>(sg, (size_t)P.mx, d, (size_t)P.sy, P.mx, rows);
+      CK(cudaGetLastError());
+      CK(cudaMemcpyAsync(h, sg, bytes, kind, st));
+    }
+    S.launches++;
   } else if (kind == cudaMemcpyHostToDevice) {
     CK(cudaMemcpy2DAsync(d, P.sy * sizeof(double), h, P.mx * sizeof(double), P.mx * sizeof(double), rows, kind, st));
   } else {
@@ -1548,7 +1583,9 @@ extern "C" void load_farray_c(void) {
     for (int k = 0; k < S.P.nvar; ++k)
       copy_rows(S.f[S.cur], S.host_f, ((size_t)k * S.P.mz + NG) * S.P.my, (size_t)S.P.nz * S.P.my, cudaMemcpyHostToDevice, S.stream);
   } else {
+    g_stage = (S.nranks == 1);
     copy_rows(S.f[S.cur], S.host_f, 0, (size_t)S.P.my * S.P.mz * S.P.nvar, cudaMemcpyHostToDevice, S.stream);
+    g_stage = false;
   }
   S.in_load = true;
   update_ghosts(S.f[S.cur], S.stream);
@@ -1560,7 +1597,9 @@ FTN_ALIAS(load_farray_c)
 extern "C" void copy_farray_c(double *f) {
   need_init("copy_farray_c");
   wait_halo(S.stream);
+  g_stage = (S.nranks == 1 && !S.loopback);
   copy_rows(S.f[S.cur], f, 0, (size_t)S.P.my * S.P.mz * S.P.nvar, cudaMemcpyDeviceToHost, S.stream);
+  g_stage = false;
   SYNC_STREAM((S.stream));
 }
 FTN_ALIAS(copy_farray_c)
