@@ -1548,11 +1548,20 @@ static void copy_rows(double *dev, double *host, size_t row0, size_t rows, cudaM
   const Pars &P = S.P;
   double *d = dev + row0 * P.sy, *h = host + row0 * P.mx;
   const size_t bytes = rows * P.mx * sizeof(double);
+  bool staged = P.sy != P.mx && g_stage && bytes >= (1u << 20) && (row0 + rows) * P.mx <= S.nreal && staged_copy_enabled();
+  if (staged && !S.stage) { // no room for the image (very large single-GPU grids): stay with the direct 2-D copies
+    static bool failed = false;
+    if (failed || cudaMalloc(&S.stage, S.nreal * sizeof(double)) != cudaSuccess) {
+      (void)cudaGetLastError();
+      S.stage = nullptr;
+      failed = true;
+      staged = false;
+    }
+  }
   if (P.sy == P.mx) {
     if (kind == cudaMemcpyHostToDevice) CK(cudaMemcpyAsync(d, h, rows * P.mx * sizeof(double), kind, st));
     else CK(cudaMemcpyAsync(h, d, rows * P.mx * sizeof(double), kind, st));
-  } else if (g_stage && bytes >= (1u << 20) && (row0 + rows) * P.mx <= S.nreal && staged_copy_enabled()) {
-    if (!S.stage) CK(cudaMalloc(&S.stage, S.nreal * sizeof(double)));
+  } else if (staged) {
     double *sg = S.stage + row0 * P.mx; // the host rows' own place in the linear image
     const unsigned grid = (unsigned)std::min<size_t>(rows, (size_t)148 * 32);
     if (kind == cudaMemcpyHostToDevice) {
