@@ -42,6 +42,14 @@ def test_helical_mhdturb_series_snapshot_and_averages(oracle_mod):
                 assert "%.3E" % math.sqrt((b.mean(axis=axes) ** 2).sum(0).mean()) == row[name], name
             if it == 6:  # 4th record of xyaverages.dat, t = 0.24
                 assert ["%g" % v for v in b[1].mean(axis=(1, 2))[:4]] == g["bymz_rec3_z0to3"]
+        if it in (0, 3):  # records 0 and 1 of yaverages.dat / zaverages.dat (d2davg = 0.1: t = 0 and t = 0.12)
+            bymxy = (_curl(o, f, iax)[1]).mean(axis=0)           # [y][x]
+            assert ["%g" % v for v in bymxy[4:9, 10]] == g["bymxy_rec%d_x10_y4to8" % (it // 3)]
+            if it == 3:
+                bz = _curl(o, f, iax)[2]
+                assert ["%g" % v for v in bz[0, 4:9, 13]] == g["bb3_xy_rec1_y4to8_x13"]  # slice_bb3.xy (z = z(n1))
+                ux2mxz = (f[iux][I] ** 2).mean(axis=1)           # [z][x]
+                assert ["%g" % v for v in ux2mxz[4:9, 10]] == g["ux2mxz_rec1_x10_z4to8"]
         phase, kvec, phi = fs.draw()
         frc = o.forcing_coefs(hm.FORCE, hm.RELHEL, fs.kav, 1.0, dt, kvec, phase, phi)
         dt, t, d = o.time_step(f, df, False, dt, t, forcing=frc, diag=it in rows)
